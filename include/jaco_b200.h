@@ -1,0 +1,85 @@
+/* jaco_b200.h -- C ABI of the B200 batched Jaco simulator (libjaco_b200.so).
+ *
+ * The reference has no FFI: its seam is the Python class JacoMujocoEnv
+ * (/root/reference/env_script/env_mujoco.py:9-167).  Each entry point below replaces the part of that class
+ * (and of the objects beneath it) named in its comment; mujoco_jaco_b200/env.py binds them with ctypes and
+ * rebuilds the reference's Python surface on top.  See INTEGRATION.md for the reference-side stub.
+ *
+ * Conventions: return 0 on success, a negative JACO_E* code otherwise (never throws); every device pointer is
+ * owned by the caller, contiguous fp32 / uint8 row-major with the leading dimension n_envs; the library owns
+ * the SoA simulation state; all calls are asynchronous and ordered on `stream` (a cudaStream_t passed as
+ * void*, NULL = legacy default stream); one host thread per handle.  There is no CPU fallback.
+ */
+#ifndef JACO_B200_H
+#define JACO_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define JACO_NQ 23
+#define JACO_NV 21
+#define JACO_NU 9
+#define JACO_NOBS 26
+#define JACO_NACT 7
+#define JACO_NAUX 72
+#define JACO_NSTATS 16
+
+enum { JACO_OK = 0, JACO_EINVAL = -1, JACO_ECUDA = -2, JACO_ENOMEM = -3 };
+/* task ids: argparser.py --task */
+enum { JACO_REACHING = 0, JACO_GRASPING = 1, JACO_PICKING = 2, JACO_PLACING = 3, JACO_PICKANDPLACE = 4 };
+/* variant = observation variant (0 env_mujoco_util.py, 1 _cis, 2 _trans) | obs_mode << 4
+ * obs_mode: 0 reaching goal (util:255-270), 1 rule-based subgoal (util:240-254, what main.py uses), 2 subgoal_obs */
+
+typedef struct jaco_sim_handle* jaco_handle;
+
+/* JacoMujocoEnvUtil.__init__ (util:15-70): model load + sim + controller, for n_envs envs on `device`.
+ * model_blob: float64 array produced by mujoco_jaco_b200/model/compiler.py (include/jaco_model_layout.h).
+ * env_offset: index of this handle's first env in the global env numbering (RNG streams; multi-GPU sharding). */
+int jaco_create(const void* model_blob, size_t nbytes, int n_envs, int task_id, int variant, int device,
+                uint64_t seed, int env_offset, jaco_handle* out);
+void jaco_destroy(jaco_handle h);
+const char* jaco_last_error(jaco_handle h);
+
+/* JacoMujocoEnv.reset (env_mujoco.py:99-102 -> util:92-174).  mask: device uint8[n] or NULL (= all envs).
+ * obs: device float[n,26] or NULL. */
+int jaco_reset(jaco_handle h, const uint8_t* mask, float* obs, void* stream);
+
+/* JacoMujocoEnv.step (env_mujoco.py:116-139): clip, take_action, 50 x (OSC + mj_step), obs, reward, terminal.
+ * action float[n,7]; obs float[n,26]; reward float[n]; done/succ uint8[n]; wb float[n] (get_wb()).
+ * auto_reset != 0: finished envs are re-initialised in the same launch and `obs` holds the new episode's
+ * first observation (VecEnv convention); the terminal observation is written to term_obs if non-NULL. */
+int jaco_step(jaco_handle h, const float* action, float* obs, float* reward, uint8_t* done, uint8_t* succ,
+              float* wb, float* term_obs, int auto_reset, void* stream);
+
+/* Same call with HOST buffers (the reference-facing path: numpy in, numpy out).  Copies the action to the
+ * device, steps, copies the results back and synchronises the stream before returning. */
+int jaco_step_host(jaco_handle h, const float* action, float* obs, float* reward, uint8_t* done, uint8_t* succ,
+                   float* wb, int auto_reset, void* stream);
+
+/* mjData state exchange (mujoco.py:217-246,332-359 teleports / MjSimState): qpos float[n,23], qvel float[n,21],
+ * aux float[n,72] (env-logic state: target, gripper, goals, counters, warm start, lagged controller state).
+ * Any pointer may be NULL. */
+int jaco_get_state(jaco_handle h, float* qpos, float* qvel, float* aux, void* stream);
+int jaco_set_state(jaco_handle h, const float* qpos, const float* qvel, const float* aux, void* stream);
+
+/* One raw mj_step with explicit ctrl float[n,9] (mujoco.py:258-278 send_forces); debug outputs, nullable:
+ * ncon int32[n], sensordata float[n,20], qacc float[n,21]. */
+int jaco_debug_substep(jaco_handle h, const float* ctrl, int32_t* ncon, float* sensordata, float* qacc,
+                       void* stream);
+
+/* Episode statistics accumulated on the device since the last call with clear != 0: out float[16] =
+ * {episodes, successes, return_sum, timeouts, drops, singular_exits, nan_resets, env_steps, length_sum, 0...}.
+ * This is the vector the multi-GPU harness all-reduces (env_mujoco.py:129-135 success-rate log). */
+int jaco_stats(jaco_handle h, float* out16, int clear, void* stream);
+
+int jaco_n_envs(jaco_handle h);
+/* number of kernels this handle has launched (bench.py "gpu_launches") */
+long long jaco_launch_count(jaco_handle h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

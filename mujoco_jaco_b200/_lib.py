@@ -1,0 +1,65 @@
+"""Loader for libjaco_b200.so (the C ABI in include/jaco_b200.h).  Fails loudly: there is no CPU fallback."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REPO = os.path.dirname(HERE)
+SO_PATH = os.path.join(HERE, "libjaco_b200.so")
+SOURCES = [os.path.join(HERE, "csrc", f) for f in ("jaco_kernels.cu", "jaco_sim.cuh", "jaco_model.h")] + [
+    os.path.join(REPO, "include", "jaco_b200.h"), os.path.join(REPO, "include", "jaco_model_layout.h")]
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-shared", "-Xcompiler", "-fPIC"]
+
+SYMBOLS = ["jaco_create", "jaco_destroy", "jaco_last_error", "jaco_reset", "jaco_step", "jaco_step_host",
+           "jaco_get_state", "jaco_set_state", "jaco_debug_substep", "jaco_stats", "jaco_n_envs", "jaco_launch_count"]
+
+
+def needs_build():
+    if not os.path.exists(SO_PATH):
+        return True
+    t = os.path.getmtime(SO_PATH)
+    return any(os.path.exists(s) and os.path.getmtime(s) > t for s in SOURCES)
+
+
+def build(force=False, verbose=False):
+    """Compile the CUDA extension in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
+    if not force and not needs_build():
+        return SO_PATH
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", SO_PATH, SOURCES[0]]
+    subprocess.check_call(cmd)
+    return SO_PATH
+
+
+_lib = None
+
+
+def load():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(SO_PATH):
+        raise RuntimeError(
+            f"{SO_PATH} is missing: the CUDA extension has not been built (run `python -c 'import __graft_entry__ as g; "
+            "g.build()'`).  mujoco_jaco_b200 has no CPU fallback.")
+    L = C.CDLL(SO_PATH)
+    vp, f, u8 = C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_uint8)
+    L.jaco_create.argtypes = [vp, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_int, C.POINTER(vp)]
+    L.jaco_destroy.argtypes = [vp]
+    L.jaco_destroy.restype = None
+    L.jaco_last_error.argtypes = [vp]
+    L.jaco_last_error.restype = C.c_char_p
+    L.jaco_reset.argtypes = [vp, vp, vp, vp]
+    L.jaco_step.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, C.c_int, vp]
+    L.jaco_step_host.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int, vp]
+    L.jaco_get_state.argtypes = [vp, vp, vp, vp, vp]
+    L.jaco_set_state.argtypes = [vp, vp, vp, vp, vp]
+    L.jaco_debug_substep.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.jaco_stats.argtypes = [vp, vp, C.c_int, vp]
+    L.jaco_n_envs.argtypes = [vp]
+    L.jaco_launch_count.argtypes = [vp]
+    L.jaco_launch_count.restype = C.c_longlong
+    _lib = L
+    return L

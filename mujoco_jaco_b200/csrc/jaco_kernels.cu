@@ -1,0 +1,197 @@
+// jaco_kernels.cu -- CUDA kernels (sm_100a) and the C ABI of libjaco_b200.so (include/jaco_b200.h).
+// One thread advances one environment through a whole env step (50 fused physics substeps); state is SoA in
+// HBM so every load/store of a warp is one coalesced 128-byte line per state row; model constants sit in
+// __constant__ memory (uniform broadcast reads).  See DESIGN.md for the layout and the roofline.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <string.h>
+#include <new>
+#include "../../include/jaco_b200.h"
+#include "jaco_sim.cuh"
+
+#define JACO_BLOCK 128
+
+struct jaco_sim_handle {
+  int n, device, env_offset;
+  JacoCfg cfg;
+  float* state;       // [JACO_NSTATE][n]
+  float* stats;       // [16]
+  float *s_action, *s_obs, *s_reward, *s_wb; unsigned char *s_done, *s_succ;  // staging for jaco_step_host
+  long long launches;
+  char err[256];
+};
+
+__device__ __forceinline__ void block_stats_flush(float* local, float* gstats) {
+  // warp-shuffle reduction of the per-thread counters, one atomic per warp per non-zero counter
+#pragma unroll
+  for (int k = 0; k < 9; k++) {
+    float v = local[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0 && v != 0.0f) atomicAdd(gstats + k, v);
+  }
+}
+
+__global__ void __launch_bounds__(JACO_BLOCK) jaco_reset_kernel(JacoCfg cfg, float* state, int N, int env_offset, const unsigned char* mask, float* obs) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  if (mask && !mask[i]) return;
+  entry_reset(cfg, state, N, i, env_offset + i, obs ? obs + (size_t)i * JACO_NOBS : nullptr);
+}
+
+__global__ void __launch_bounds__(JACO_BLOCK) jaco_step_kernel(JacoCfg cfg, float* state, int N, int env_offset, const float* action, float* obs, float* reward,
+                                                               unsigned char* done, unsigned char* succ, float* wb, float* term_obs, int auto_reset, float* gstats) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  float local[16];
+#pragma unroll
+  for (int k = 0; k < 16; k++) local[k] = 0;
+  if (i < N) {
+    float a[JACO_NACT];
+#pragma unroll
+    for (int k = 0; k < JACO_NACT; k++) a[k] = action[(size_t)i * JACO_NACT + k];
+    float r, w; unsigned char d, sc;
+    entry_step(cfg, state, N, i, env_offset + i, a, obs + (size_t)i * JACO_NOBS, &r, &d, &sc, &w,
+               term_obs ? term_obs + (size_t)i * JACO_NOBS : nullptr, auto_reset, local);
+    reward[i] = r; done[i] = d; succ[i] = sc; wb[i] = w;
+  }
+  block_stats_flush(local, gstats);
+}
+
+__global__ void __launch_bounds__(JACO_BLOCK) jaco_substep_kernel(float* state, int N, const float* ctrl, int* ncon, float* sensordata, float* qacc) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  float c[JACO_NU];
+  for (int k = 0; k < JACO_NU; k++) c[k] = ctrl[(size_t)i * JACO_NU + k];
+  entry_substep(state, N, i, c, ncon ? ncon + i : nullptr, sensordata ? sensordata + (size_t)i * 20 : nullptr, qacc ? qacc + (size_t)i * JACO_NV : nullptr);
+}
+
+// row-major API tensors <-> SoA state rows
+__global__ void jaco_gather_kernel(const float* state, int N, int row0, int nrows, float* out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  for (int r = 0; r < nrows; r++) out[(size_t)i * nrows + r] = state[(size_t)(row0 + r) * N + i];
+}
+__global__ void jaco_scatter_kernel(float* state, int N, int row0, int nrows, const float* in) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  for (int r = 0; r < nrows; r++) state[(size_t)(row0 + r) * N + i] = in[(size_t)i * nrows + r];
+}
+
+#define CK(call)                                                                                     \
+  do {                                                                                               \
+    cudaError_t e_ = (call);                                                                         \
+    if (e_ != cudaSuccess) { snprintf(h->err, sizeof h->err, "%s: %s", #call, cudaGetErrorString(e_)); return JACO_ECUDA; } \
+  } while (0)
+
+extern "C" {
+
+int jaco_create(const void* model_blob, size_t nbytes, int n_envs, int task_id, int variant, int device, uint64_t seed, int env_offset, jaco_handle* out) {
+  if (!model_blob || !out || n_envs <= 0 || nbytes != sizeof(double) * JM_TOTAL || task_id < 0 || task_id > 4) return JACO_EINVAL;
+  jaco_sim_handle* h = new (std::nothrow) jaco_sim_handle();
+  if (!h) return JACO_ENOMEM;
+  memset(h, 0, sizeof *h);
+  *out = h;
+  h->n = n_envs; h->device = device; h->env_offset = env_offset;
+  h->cfg.task = task_id; h->cfg.variant = variant & 15; h->cfg.obs_mode = (variant >> 4) & 15; h->cfg.seed = seed;
+  h->cfg.task_max_steps = (task_id == JACO_REACHING || task_id == JACO_GRASPING) ? 500 : ((task_id == JACO_PICKING || task_id == JACO_PLACING) ? 700 : 1200);
+  CK(cudaSetDevice(device));
+  JacoModel* m = new JacoModel();
+  jaco_model_from_blob((const double*)model_blob, m);
+  cudaError_t e = cudaMemcpyToSymbol(c_jaco_model, m, sizeof(JacoModel));
+  delete m;
+  CK(e);
+  CK(cudaMalloc(&h->state, sizeof(float) * JACO_NSTATE * (size_t)n_envs));
+  CK(cudaMemset(h->state, 0, sizeof(float) * JACO_NSTATE * (size_t)n_envs));
+  CK(cudaMalloc(&h->stats, sizeof(float) * JACO_NSTATS));
+  CK(cudaMemset(h->stats, 0, sizeof(float) * JACO_NSTATS));
+  CK(cudaFuncSetAttribute(jaco_step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 0));
+  CK(cudaFuncSetAttribute(jaco_reset_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 0));
+  return JACO_OK;
+}
+
+void jaco_destroy(jaco_handle h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  cudaFree(h->state); cudaFree(h->stats);
+  cudaFree(h->s_action); cudaFree(h->s_obs); cudaFree(h->s_reward); cudaFree(h->s_wb); cudaFree(h->s_done); cudaFree(h->s_succ);
+  delete h;
+}
+const char* jaco_last_error(jaco_handle h) { return h ? h->err : "null handle"; }
+int jaco_n_envs(jaco_handle h) { return h ? h->n : 0; }
+long long jaco_launch_count(jaco_handle h) { return h ? h->launches : 0; }
+
+static inline int nblocks(int n) { return (n + JACO_BLOCK - 1) / JACO_BLOCK; }
+
+int jaco_reset(jaco_handle h, const uint8_t* mask, float* obs, void* stream) {
+  if (!h) return JACO_EINVAL;
+  jaco_reset_kernel<<<nblocks(h->n), JACO_BLOCK, 0, (cudaStream_t)stream>>>(h->cfg, h->state, h->n, h->env_offset, mask, obs);
+  h->launches++;
+  CK(cudaGetLastError());
+  return JACO_OK;
+}
+
+int jaco_step(jaco_handle h, const float* action, float* obs, float* reward, uint8_t* done, uint8_t* succ, float* wb, float* term_obs, int auto_reset, void* stream) {
+  if (!h || !action || !obs || !reward || !done || !succ || !wb) return JACO_EINVAL;
+  jaco_step_kernel<<<nblocks(h->n), JACO_BLOCK, 0, (cudaStream_t)stream>>>(h->cfg, h->state, h->n, h->env_offset, action, obs, reward, done, succ, wb, term_obs, auto_reset, h->stats);
+  h->launches++;
+  CK(cudaGetLastError());
+  return JACO_OK;
+}
+
+int jaco_step_host(jaco_handle h, const float* action, float* obs, float* reward, uint8_t* done, uint8_t* succ, float* wb, int auto_reset, void* stream) {
+  if (!h || !action || !obs || !reward || !done || !succ || !wb) return JACO_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  size_t n = h->n;
+  if (!h->s_action) {
+    CK(cudaMalloc(&h->s_action, n * JACO_NACT * sizeof(float))); CK(cudaMalloc(&h->s_obs, n * JACO_NOBS * sizeof(float)));
+    CK(cudaMalloc(&h->s_reward, n * sizeof(float))); CK(cudaMalloc(&h->s_wb, n * sizeof(float)));
+    CK(cudaMalloc(&h->s_done, n)); CK(cudaMalloc(&h->s_succ, n));
+  }
+  CK(cudaMemcpyAsync(h->s_action, action, n * JACO_NACT * sizeof(float), cudaMemcpyHostToDevice, st));
+  int rc = jaco_step(h, h->s_action, h->s_obs, h->s_reward, h->s_done, h->s_succ, h->s_wb, nullptr, auto_reset, stream);
+  if (rc) return rc;
+  CK(cudaMemcpyAsync(obs, h->s_obs, n * JACO_NOBS * sizeof(float), cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(reward, h->s_reward, n * sizeof(float), cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(wb, h->s_wb, n * sizeof(float), cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(done, h->s_done, n, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(succ, h->s_succ, n, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return JACO_OK;
+}
+
+int jaco_get_state(jaco_handle h, float* qpos, float* qvel, float* aux, void* stream) {
+  if (!h) return JACO_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  int nb = (h->n + 255) / 256;
+  if (qpos) { jaco_gather_kernel<<<nb, 256, 0, st>>>(h->state, h->n, 0, JACO_NQ, qpos); h->launches++; }
+  if (qvel) { jaco_gather_kernel<<<nb, 256, 0, st>>>(h->state, h->n, JACO_NQ, JACO_NV, qvel); h->launches++; }
+  if (aux) { jaco_gather_kernel<<<nb, 256, 0, st>>>(h->state, h->n, JACO_NQ + JACO_NV, JACO_NAUX, aux); h->launches++; }
+  CK(cudaGetLastError());
+  return JACO_OK;
+}
+int jaco_set_state(jaco_handle h, const float* qpos, const float* qvel, const float* aux, void* stream) {
+  if (!h) return JACO_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  int nb = (h->n + 255) / 256;
+  if (qpos) { jaco_scatter_kernel<<<nb, 256, 0, st>>>(h->state, h->n, 0, JACO_NQ, qpos); h->launches++; }
+  if (qvel) { jaco_scatter_kernel<<<nb, 256, 0, st>>>(h->state, h->n, JACO_NQ, JACO_NV, qvel); h->launches++; }
+  if (aux) { jaco_scatter_kernel<<<nb, 256, 0, st>>>(h->state, h->n, JACO_NQ + JACO_NV, JACO_NAUX, aux); h->launches++; }
+  CK(cudaGetLastError());
+  return JACO_OK;
+}
+int jaco_debug_substep(jaco_handle h, const float* ctrl, int32_t* ncon, float* sensordata, float* qacc, void* stream) {
+  if (!h || !ctrl) return JACO_EINVAL;
+  jaco_substep_kernel<<<nblocks(h->n), JACO_BLOCK, 0, (cudaStream_t)stream>>>(h->state, h->n, ctrl, ncon, sensordata, qacc);
+  h->launches++;
+  CK(cudaGetLastError());
+  return JACO_OK;
+}
+int jaco_stats(jaco_handle h, float* out16, int clear, void* stream) {
+  if (!h || !out16) return JACO_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  CK(cudaMemcpyAsync(out16, h->stats, sizeof(float) * JACO_NSTATS, cudaMemcpyDeviceToDevice, st));
+  if (clear) CK(cudaMemsetAsync(h->stats, 0, sizeof(float) * JACO_NSTATS, st));
+  return JACO_OK;
+}
+
+}  // extern "C"

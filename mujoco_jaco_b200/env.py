@@ -1,0 +1,248 @@
+"""Host-side mirror of the reference's environment surface on top of the C ABI.
+
+* JacoVecEnv   -- n_envs environments resident on one B200; torch tensors in / out, stream ordered.
+* JacoMujocoEnv -- the reference's single-env class (env_script/env_mujoco.py:9-167) with the same constructor
+  kwargs, attributes and return types (numpy obs f32[26], float reward, bool done, {0: 0}), so that
+  main.py:48,254,260 and the stable-baselines HPC loop can drive it unchanged.
+PyTorch is used for device memory and streams only; all arithmetic happens in libjaco_b200.so.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+import torch
+
+from . import _lib
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+NQ, NV, NU, NOBS, NACT, NAUX, NSTATS = 23, 21, 9, 26, 7, 72, 16
+TASKS = {"reaching": 0, "grasping": 1, "picking": 2, "placing": 3, "pickAndplace": 4}
+VARIANTS = {"base": 0, "cis": 1, "trans": 2}
+STAT_NAMES = ["episodes", "successes", "return_sum", "timeouts", "drops", "singular_exits", "nan_resets",
+              "env_steps", "length_sum"]
+
+
+def load_model_blob(robot_file="jaco2_curtain_torque"):
+    path = os.path.join(HERE, "model", robot_file + ".npz")
+    if not os.path.exists(path):
+        raise NotImplementedError(f"no compiled model for robot_file={robot_file!r} ({path}); run "
+                                  "python -m mujoco_jaco_b200.model.compiler <xml>")
+    return np.ascontiguousarray(np.load(path)["blob"], dtype=np.float64)
+
+
+def _ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+class JacoVecEnv:
+    """Batched Jaco environment on one GPU (one independent shard of the global env range)."""
+
+    def __init__(self, n_envs, task="picking", variant="base", obs_mode=1, seed=0, device=0, env_offset=0,
+                 robot_file="jaco2_curtain_torque", auto_reset=True):
+        if not torch.cuda.is_available():
+            raise RuntimeError("JacoVecEnv needs a CUDA device: mujoco_jaco_b200 has no CPU fallback")
+        if task not in TASKS:
+            raise NotImplementedError(f"task {task!r}")
+        self.L = _lib.load()
+        self.n_envs, self.task, self.auto_reset = int(n_envs), task, auto_reset
+        self.device = torch.device("cuda", device)
+        blob = load_model_blob(robot_file)
+        h = C.c_void_p()
+        rc = self.L.jaco_create(blob.ctypes.data_as(C.c_void_p), blob.nbytes, self.n_envs, TASKS[task],
+                                VARIANTS[variant] | (obs_mode << 4), device, seed, env_offset, C.byref(h))
+        if rc != 0:
+            msg = self.L.jaco_last_error(h).decode() if h else ""
+            raise RuntimeError(f"jaco_create failed ({rc}) {msg}")
+        self.h = h
+        n, dev = self.n_envs, self.device
+        self.obs = torch.zeros(n, NOBS, device=dev)
+        self.reward = torch.zeros(n, device=dev)
+        self.done = torch.zeros(n, dtype=torch.uint8, device=dev)
+        self.succ = torch.zeros(n, dtype=torch.uint8, device=dev)
+        self.wb = torch.zeros(n, device=dev)
+        self._stats = torch.zeros(NSTATS, device=dev)
+
+    def _check(self, rc):
+        if rc != 0:
+            raise RuntimeError(f"libjaco_b200 call failed ({rc}): {self.L.jaco_last_error(self.h).decode()}")
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.jaco_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def reset(self, mask=None):
+        if mask is not None:
+            mask = mask.to(self.device, torch.uint8).contiguous()
+        self._check(self.L.jaco_reset(self.h, _ptr(mask), _ptr(self.obs), self._stream()))
+        return self.obs
+
+    def step(self, action, term_obs=None):
+        """action: float32 cuda tensor [n,7] (or [n,6] for reaching).  Returns views of the env's own buffers."""
+        a = action
+        if a.shape[1] != NACT:
+            a = torch.nn.functional.pad(a, (0, NACT - a.shape[1]))
+        a = a.to(self.device, torch.float32).contiguous()
+        self._check(self.L.jaco_step(self.h, _ptr(a), _ptr(self.obs), _ptr(self.reward), _ptr(self.done), _ptr(self.succ),
+                                     _ptr(self.wb), _ptr(term_obs), int(self.auto_reset), self._stream()))
+        return self.obs, self.reward, self.done, self.succ
+
+    def step_host(self, action_np, out=None):
+        """Reference-facing path: host (numpy / pinned) buffers in and out, copies inside the call."""
+        a = np.ascontiguousarray(action_np, np.float32)
+        if out is None:
+            out = (np.empty((self.n_envs, NOBS), np.float32), np.empty(self.n_envs, np.float32),
+                   np.empty(self.n_envs, np.uint8), np.empty(self.n_envs, np.uint8), np.empty(self.n_envs, np.float32))
+        obs, rew, done, succ, wb = out
+        vp = lambda x: x.ctypes.data_as(C.c_void_p)
+        self._check(self.L.jaco_step_host(self.h, vp(a), vp(obs), vp(rew), vp(done), vp(succ), vp(wb),
+                                          int(self.auto_reset), self._stream()))
+        return out
+
+    def get_state(self):
+        n, dev = self.n_envs, self.device
+        q, v, a = torch.empty(n, NQ, device=dev), torch.empty(n, NV, device=dev), torch.empty(n, NAUX, device=dev)
+        self._check(self.L.jaco_get_state(self.h, _ptr(q), _ptr(v), _ptr(a), self._stream()))
+        return q, v, a
+
+    def set_state(self, qpos=None, qvel=None, aux=None):
+        f = lambda t: None if t is None else t.to(self.device, torch.float32).contiguous()
+        q, v, a = f(qpos), f(qvel), f(aux)
+        if a is not None and a.shape[1] != NAUX:
+            a = torch.nn.functional.pad(a, (0, NAUX - a.shape[1]))
+        self._check(self.L.jaco_set_state(self.h, _ptr(q), _ptr(v), _ptr(a), self._stream()))
+        torch.cuda.current_stream(self.device).synchronize()  # keep q/v/a alive until consumed
+
+    def debug_substep(self, ctrl):
+        n, dev = self.n_envs, self.device
+        c = ctrl.to(dev, torch.float32).contiguous()
+        ncon = torch.zeros(n, dtype=torch.int32, device=dev)
+        sd, qacc = torch.zeros(n, 20, device=dev), torch.zeros(n, NV, device=dev)
+        self._check(self.L.jaco_debug_substep(self.h, _ptr(c), _ptr(ncon), _ptr(sd), _ptr(qacc), self._stream()))
+        return ncon, sd, qacc
+
+    def stats(self, clear=True):
+        """Device-side episode counters (float[16] on the GPU): what the multi-GPU harness all-reduces."""
+        self._check(self.L.jaco_stats(self.h, _ptr(self._stats), int(clear), self._stream()))
+        return self._stats
+
+    def launch_count(self):
+        return int(self.L.jaco_launch_count(self.h))
+
+
+class _Box:
+    """Minimal stand-in for gym.spaces.Box (gym is optional at run time)."""
+
+    def __init__(self, low, high, dtype=np.float32):
+        self.low, self.high = np.asarray(low, dtype), np.asarray(high, dtype)
+        self.shape, self.dtype = self.low.shape, dtype
+
+    def sample(self):
+        return np.random.uniform(self.low, self.high).astype(self.dtype)
+
+    def contains(self, x):
+        x = np.asarray(x)
+        return x.shape == self.shape and bool(np.all(x >= self.low) and np.all(x <= self.high))
+
+
+def _box(low, high):
+    try:
+        from gym import spaces  # type: ignore
+        return spaces.Box(low, high, dtype=np.float32)
+    except Exception:
+        return _Box(low, high)
+
+
+class JacoMujocoEnv:
+    """Drop-in for env_script.env_mujoco.JacoMujocoEnv (n_envs = 1 on the GPU)."""
+
+    def __init__(self, **kwargs):
+        self.n_robots = kwargs.get("n_robots", 1)
+        if self.n_robots != 1:
+            raise NotImplementedError("\n\t\033[91m[ERROR]: xml_file of the given number of robots doesn't exist\033[0m")
+        robot_file = kwargs.get("robot_file", "jaco2_curtain_torque") or "jaco2_curtain_torque"
+        self.task = kwargs.get("task", None)
+        obs_mode = 2 if kwargs.get("subgoal_obs", False) else (1 if kwargs.get("rulebased_subgoal", False) else 0)
+        seed = kwargs.get("seed", 0) or 0
+        self._vec = JacoVecEnv(1, task=self.task, variant=kwargs.get("variant", "base"), obs_mode=obs_mode, seed=int(seed),
+                               device=kwargs.get("device", 0), robot_file=robot_file, auto_reset=False)
+        self.current_steps, self.max_steps = 0, 2500
+        if self.task in ["reaching", "grasping", "carrying", "releasing", "pushing"]:
+            self.task_max_steps = 500
+        elif self.task in ["picking", "placing"]:
+            self.task_max_steps = 700
+        else:
+            self.task_max_steps = 1200
+        self.skip_frames = 50
+        logger_path = kwargs.get("logger_path", "./logger_csv")
+        os.makedirs(logger_path, exist_ok=True)
+        self.file_logger = open(logger_path + "/SR_" + self.task + "_abalation_GA_learned_2.csv", "w")
+        obs_max = np.hstack([[3], [1] * 25]).astype(np.float32)
+        self.observation_space = _box(-obs_max, obs_max)
+        try:
+            self.state_shape = kwargs["stateGen"].get_state_shape()
+        except Exception:
+            self.state_shape = self.observation_space.shape[0]
+        self.pose_action_space_max, self.gripper_action_space_max, self.gripper_action_space_min = 1, 1, -1
+        nact = 6 if self.task in ["reaching", "pushing"] else 7
+        self.act_max, self.act_min = np.ones(nact), -np.ones(nact)
+        self.action_space = _box(self.act_min, self.act_max)
+        self.wb, self.accum_rew, self.accum_succ, self.metadata, self.log_save = 0, 0, [0] * 25, None, False
+        self.verbose = kwargs.get("verbose", True)
+        self.reset()
+
+    def reset(self):
+        self.current_steps, self.accum_rew = 0, 0
+        return self._vec.reset().cpu().numpy()[0].copy()
+
+    def get_state_shape(self):
+        return self.state_shape
+
+    def get_num_observation(self):
+        return self.observation_space.shape[0]
+
+    def get_num_action(self):
+        return self.action_space.shape[0]
+
+    def get_action_bound(self):
+        return self.pose_action_space_max
+
+    def step(self, action, weight=None, subgoal=None, id=None):
+        action = np.clip(np.asarray(action, np.float32), self.act_min, self.act_max)
+        a = np.zeros((1, NACT), np.float32)
+        a[0, : len(action)] = action
+        obs, rew, done, succ, wb = self._vec.step_host(a)
+        self.current_steps += 1
+        total_reward, done, self.wb = float(rew[0]), bool(done[0]), float(wb[0])
+        self.accum_rew += total_reward
+        if done:
+            self.accum_succ.pop()
+            self.accum_succ.insert(0, int(succ[0]))
+            sr = "{0:3.3f}".format(sum(self.accum_succ) / 25 * 100)
+            if self.verbose:
+                print("sr: ", sr)
+                print("Return: ", self.accum_rew)
+            self.file_logger.writelines(sr + "\n")
+            self.file_logger.flush()
+        assert self.state_shape == obs.shape[1]
+        return obs[0].copy(), total_reward, done, {0: 0}
+
+    def get_wb(self):
+        return self.wb
+
+    def seed(self, seed):
+        pass
+
+    def close(self):
+        self._vec.close()
+        return None
+
+    def set_capture_path(self, path):
+        raise NotImplementedError("viewer / GL capture: unavailable on this box")

