@@ -79,6 +79,9 @@ int jaco_n_envs(jaco_handle h);
 /* number of kernels this handle has launched (bench.py "gpu_launches") */
 long long jaco_launch_count(jaco_handle h);
 
+/* FP32 FMA peak of `device` in TFLOP/s, measured with a register-resident FMA loop (roofline denominator). */
+double jaco_fp32_peak_tflops(int device, int reps);
+
 #ifdef __cplusplus
 }
 #endif

@@ -13,7 +13,7 @@ SOURCES = [os.path.join(HERE, "csrc", f) for f in ("jaco_kernels.cu", "jaco_sim.
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-shared", "-Xcompiler", "-fPIC"]
 
 SYMBOLS = ["jaco_create", "jaco_destroy", "jaco_last_error", "jaco_reset", "jaco_step", "jaco_step_host",
-           "jaco_get_state", "jaco_set_state", "jaco_debug_substep", "jaco_stats", "jaco_n_envs", "jaco_launch_count"]
+           "jaco_get_state", "jaco_set_state", "jaco_debug_substep", "jaco_stats", "jaco_n_envs", "jaco_launch_count", "jaco_fp32_peak_tflops"]
 
 
 def needs_build():
@@ -61,5 +61,7 @@ def load():
     L.jaco_n_envs.argtypes = [vp]
     L.jaco_launch_count.argtypes = [vp]
     L.jaco_launch_count.restype = C.c_longlong
+    L.jaco_fp32_peak_tflops.argtypes = [C.c_int, C.c_int]
+    L.jaco_fp32_peak_tflops.restype = C.c_double
     _lib = L
     return L

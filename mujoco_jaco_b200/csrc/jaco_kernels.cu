@@ -77,6 +77,20 @@ __global__ void jaco_scatter_kernel(float* state, int N, int row0, int nrows, co
   for (int r = 0; r < nrows; r++) state[(size_t)(row0 + r) * N + i] = in[(size_t)i * nrows + r];
 }
 
+// FP32 FMA peak micro-benchmark: the denominator of the step kernel's compute roofline
+__global__ void __launch_bounds__(256) jaco_fma_peak_kernel(float* out, int iters) {
+  float x = 1.0f + 1e-7f * threadIdx.x, y = 1e-9f * blockIdx.x;
+  float a0 = 0.1f, a1 = 0.2f, a2 = 0.3f, a3 = 0.4f, a4 = 0.5f, a5 = 0.6f, a6 = 0.7f, a7 = 0.8f;
+  for (int i = 0; i < iters; i++) {
+#pragma unroll
+    for (int u = 0; u < 16; u++) {
+      a0 = fmaf(a0, x, y); a1 = fmaf(a1, x, y); a2 = fmaf(a2, x, y); a3 = fmaf(a3, x, y);
+      a4 = fmaf(a4, x, y); a5 = fmaf(a5, x, y); a6 = fmaf(a6, x, y); a7 = fmaf(a7, x, y);
+    }
+  }
+  out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+
 #define CK(call)                                                                                     \
   do {                                                                                               \
     cudaError_t e_ = (call);                                                                         \
@@ -192,6 +206,26 @@ int jaco_stats(jaco_handle h, float* out16, int clear, void* stream) {
   CK(cudaMemcpyAsync(out16, h->stats, sizeof(float) * JACO_NSTATS, cudaMemcpyDeviceToDevice, st));
   if (clear) CK(cudaMemsetAsync(h->stats, 0, sizeof(float) * JACO_NSTATS, st));
   return JACO_OK;
+}
+
+// Measured FP32 FMA throughput of `device` in TFLOP/s (FMA = 2 flops); best of `reps` timed launches.
+double jaco_fp32_peak_tflops(int device, int reps) {
+  if (cudaSetDevice(device) != cudaSuccess) return -1.0;
+  int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+  int blocks = sms * 8, iters = 4096; float* out = nullptr;
+  if (cudaMalloc(&out, sizeof(float) * blocks * 256) != cudaSuccess) return -1.0;
+  cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+  double best = 0;
+  for (int r = 0; r < reps + 2; r++) {
+    cudaEventRecord(e0);
+    jaco_fma_peak_kernel<<<blocks, 256>>>(out, iters);
+    cudaEventRecord(e1); cudaEventSynchronize(e1);
+    float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+    double tf = 2.0 * 128.0 * iters * (double)blocks * 256 / (ms * 1e-3) / 1e12;
+    if (r >= 2 && tf > best) best = tf;
+  }
+  cudaFree(out); cudaEventDestroy(e0); cudaEventDestroy(e1);
+  return best;
 }
 
 }  // extern "C"
