@@ -654,9 +654,16 @@ JHD void geom_world(const JacoSim& s, const JacoGeom& G, float* pos, float* R) {
   float t[3]; m3mulv(t, s.bR[G.body], G.pos); v3add(pos, s.bx[G.body], t);
   m3mul(R, s.bR[G.body], G.R);
 }
+#if defined(JACO_COLLISION_STATS) && !defined(__CUDACC__)
+static long long g_cstats[16];
+#define CSTAT(i) g_cstats[i]++
+#else
+#define CSTAT(i)
+#endif
 JHD void collision(JacoSim& s) {
   const JacoModel& m = MDL;
   s.ncon = 0;
+  CSTAT(0);
   float hs[3], t[3];
   m3mulv(t, s.bR[6], m.hand_sphere); v3add(hs, s.bx[6], t);
   for (int p = 0; p < JM_NPAIR; p++) {
@@ -669,8 +676,10 @@ JHD void collision(JacoSim& s) {
       float d[3]; v3sub(d, hs, po);
       if (O.type != JACO_GEOM_PLANE) { if (v3norm(d) > m.hand_sphere[3] + O.rbound + P.margin) continue; }
       else { if (d[2] > m.hand_sphere[3] + P.margin) continue; }
+      CSTAT(P.group);
     }
     if (G1.type != JACO_GEOM_PLANE && G2.type != JACO_GEOM_PLANE) { float d[3]; v3sub(d, p1, p2); if (v3norm(d) > G1.rbound + G2.rbound + P.margin) continue; }
+    CSTAT(5 + P.group);
     float R1[9], R2[9];
     m3mul(R1, s.bR[G1.body], G1.R); m3mul(R2, s.bR[G2.body], G2.R);
     if (G1.type == JACO_GEOM_PLANE && G2.type == JACO_GEOM_BOX) collide_plane_box(s, p, p1, R1, p2, R2, G2.size, P.margin);
@@ -1355,7 +1364,8 @@ JHD float get_reward(const JacoCfg& cfg, const JacoSim& s) {  // util:312-446
     get_rotation(ev, s.gripper_pose[3], s.gripper_pose[4], s.gripper_pose[5], down, 0);
     v3sub(xyz, s.bx[10], s.gripper_pose);
     float od = v3norm(xyz), x = xyz[0] / od, z = xyz[2] / od;
-    float pitch = -acosf(z), yaw = -acosf(-x / sqrtf(1 - z * z));
+    // fp32 guard: |x| / sqrt(1 - z^2) can round past 1 when the object sits in the gripper's x-z plane (DESIGN.md "deviations")
+    float pitch = -acosf(fminf(fmaxf(z, -1.0f), 1.0f)), yaw = -acosf(fminf(fmaxf(-x / sqrtf(fmaxf(1 - z * z, 1e-30f)), -1.0f), 1.0f));
     get_rotation(tv, 0, pitch, yaw, up, 1);
     tv[2] *= -1;
     v3sub(dv, ev, tv);

@@ -968,7 +968,9 @@ static real get_reward(jo_env *e) { /* util:312-446 */
     get_rotation(ev, e->gripper_pose[3], e->gripper_pose[4], e->gripper_pose[5], down, 0);
     v3sub(xyz, e->obj_xpos, e->gripper_pose);
     real od = v3norm(xyz), x = xyz[0] / od, z = xyz[2] / od;
-    real pitch = -racos(z), yaw = -racos(-x / rsqrt_(1 - z * z));
+    real cz = z < -1 ? -1 : (z > 1 ? 1 : z), cx = -x / rsqrt_(1 - z * z > R_(1e-30) ? 1 - z * z : R_(1e-30));
+    if (cx < -1) cx = -1; if (cx > 1) cx = 1; /* rounding guard: the reference would return NaN here (measure-zero set) */
+    real pitch = -racos(cz), yaw = -racos(cx);
     get_rotation(tv, 0, pitch, yaw, up, 1);
     tv[2] *= -1;
     v3sub(dv, ev, tv);

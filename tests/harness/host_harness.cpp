@@ -2,6 +2,7 @@
 // for the CPU so that the CPU-only test-suite can check the kernel logic against the oracle on machines
 // without a GPU.  Never loaded by the product; the shipped library only launches the CUDA kernels.
 #include <string.h>
+#define JACO_COLLISION_STATS 1
 #include "../../mujoco_jaco_b200/csrc/jaco_sim.cuh"
 
 extern "C" {
@@ -41,3 +42,24 @@ void hh_osc(const float* J, const float* Mc45, const float* bias6, const float* 
   osc_generate(s, dq, u);
 }
 }
+
+// per-substep trace of one env step (debugging aid for the parity tests): out[k] = {qpos 23, qvel 21, ncon, iters, nlim}
+extern "C" void hh_step_trace(int task, int variant, unsigned long long seed, int env_id, float* state, int N, int i, const float* action, float* out47x50) {
+  JacoCfg c = mkcfg(task, variant, seed);
+  JacoSim s; load_env(state, N, i, s); refresh_lagged(s);
+  float a[7], u[6];
+  for (int k = 0; k < 7; k++) a[k] = fminf(fmaxf(action[k], -1.0f), 1.0f);
+  take_action(s, a);
+  for (int k = 0; k < 50; k++) {
+    osc_generate(s, s.qvel, u);
+    substep(s, u, k, k == 49);
+    float* o = out47x50 + 47 * k;
+    for (int j = 0; j < JACO_NQ; j++) o[j] = s.qpos[j];
+    for (int j = 0; j < JACO_NV; j++) o[23 + j] = s.qvel[j];
+    o[44] = (float)s.ncon; o[45] = (float)s.solver_iters;
+    int mask = 0; for (int c = 0; c < s.ncon; c++) { const JacoPair& P = MDL.pairs[s.cpair[c]]; int m1 = body_block(MDL.geoms[P.g1].body), m2 = body_block(MDL.geoms[P.g2].body); if (m1 && m2 && m1 != m2) mask |= (m1 | m2); }
+    o[46] = (float)(s.nlim + 100 * mask);
+  }
+}
+
+extern "C" void hh_cstats(long long* out, int clear) { for (int i = 0; i < 16; i++) { out[i] = g_cstats[i]; if (clear) g_cstats[i] = 0; } }
