@@ -42,6 +42,9 @@ def test_one_substep_state_and_contacts_picking():
     n = 512
     env = JacoVecEnv(n, task="picking", seed=9, auto_reset=False)
     env.reset()
+    # one zero-action env step first: at the reset pose the destination box touches the floor with dist == 0
+    # exactly, a knife edge on which fp32 (contact) and the fp64 oracle (no contact) legitimately differ
+    env.step(torch.zeros(n, 7, device="cuda"))
     q, v, aux = [t.cpu().numpy().astype(np.float64) for t in env.get_state()]
     rng = np.random.default_rng(1)
     v[:, :9] = rng.normal(0, 0.3, (n, 9))

@@ -99,7 +99,7 @@ def test_terminal_logic_boundaries():
     q, v, aux = hs.get_state()
     q[0, 11] = 0.05; q[0, 9:11] = [0.5, -0.5]          # env 0: object below z = 0.1 -> drop, -20
     aux[1, 9] = 699                                     # env 1: current_steps 699 -> time-out on this step, -10
-    q[2, 2] = np.pi                                     # env 2: singular posture
+    q[2, 2] = np.pi; aux[2, 46 + 2] = np.pi              # env 2: singular posture (state and lagged mjData)
     hs.set_state(q, v, aux)
     obs, rew, done, succ, wb = hs.step(np.zeros((4, 7), np.float32))
     assert done[0] == 1 and rew[0] < -19
