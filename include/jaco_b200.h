@@ -75,6 +75,9 @@ int jaco_debug_substep(jaco_handle h, const float* ctrl, int32_t* ncon, float* s
  * This is the vector the multi-GPU harness all-reduces (env_mujoco.py:129-135 success-rate log). */
 int jaco_stats(jaco_handle h, float* out16, int clear, void* stream);
 
+/* diagnostics: host copy of the step work-list counters, out int32[16] = {n_bail, n_reset of the last step,
+ * cumulative bail-reason histogram (limit, hand, forearm, object, dest, osc, nan), ...}; synchronises the device. */
+int jaco_debug_counters(jaco_handle h, int32_t* out16);
 int jaco_n_envs(jaco_handle h);
 /* number of kernels this handle has launched (bench.py "gpu_launches") */
 long long jaco_launch_count(jaco_handle h);

@@ -8,12 +8,12 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 REPO = os.path.dirname(HERE)
 SO_PATH = os.path.join(HERE, "libjaco_b200.so")
-SOURCES = [os.path.join(HERE, "csrc", f) for f in ("jaco_kernels.cu", "jaco_sim.cuh", "jaco_model.h")] + [
+SOURCES = [os.path.join(HERE, "csrc", f) for f in ("jaco_kernels.cu", "jaco_sim.cuh", "jaco_fast.cuh", "jaco_model.h")] + [
     os.path.join(REPO, "include", "jaco_b200.h"), os.path.join(REPO, "include", "jaco_model_layout.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-shared", "-Xcompiler", "-fPIC"]
 
 SYMBOLS = ["jaco_create", "jaco_destroy", "jaco_last_error", "jaco_reset", "jaco_step", "jaco_step_host",
-           "jaco_get_state", "jaco_set_state", "jaco_debug_substep", "jaco_stats", "jaco_n_envs", "jaco_launch_count", "jaco_fp32_peak_tflops"]
+           "jaco_get_state", "jaco_set_state", "jaco_debug_substep", "jaco_stats", "jaco_debug_counters", "jaco_n_envs", "jaco_launch_count", "jaco_fp32_peak_tflops"]
 
 
 def needs_build():
@@ -58,6 +58,7 @@ def load():
     L.jaco_set_state.argtypes = [vp, vp, vp, vp, vp]
     L.jaco_debug_substep.argtypes = [vp, vp, vp, vp, vp, vp]
     L.jaco_stats.argtypes = [vp, vp, C.c_int, vp]
+    L.jaco_debug_counters.argtypes = [vp, vp]
     L.jaco_n_envs.argtypes = [vp]
     L.jaco_launch_count.argtypes = [vp]
     L.jaco_launch_count.restype = C.c_longlong

@@ -5,9 +5,10 @@
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <string.h>
+#include <stdlib.h>
 #include <new>
 #include "../../include/jaco_b200.h"
-#include "jaco_sim.cuh"
+#include "jaco_fast.cuh"
 
 #define JACO_BLOCK 128
 
@@ -17,6 +18,9 @@ struct jaco_sim_handle {
   float* state;       // [JACO_NSTATE][n]
   float* stats;       // [16]
   float *s_action, *s_obs, *s_reward, *s_wb; unsigned char *s_done, *s_succ;  // staging for jaco_step_host
+  int use_fast;        // model matches the structure jaco_fast.cuh is specialised to
+  int* worklist;       // [2][n] env indices: row 0 = bailed out of the fast kernel, row 1 = finished episodes to reset
+  int* counters;       // [16]: 0 n_bail, 1 n_reset, 2.. bail-reason histogram (cumulative, diagnostics)
   long long launches;
   char err[256];
 };
@@ -53,6 +57,67 @@ __global__ void __launch_bounds__(JACO_BLOCK) jaco_step_kernel(JacoCfg cfg, floa
     entry_step(cfg, state, N, i, env_offset + i, a, obs + (size_t)i * JACO_NOBS, &r, &d, &sc, &w,
                term_obs ? term_obs + (size_t)i * JACO_NOBS : nullptr, auto_reset, local);
     reward[i] = r; done[i] = d; succ[i] = sc; wb[i] = w;
+  }
+  block_stats_flush(local, gstats);
+}
+
+// ---- two-kernel env step: fast path for every env, general path for the envs that left the fast regime ----
+#ifndef JACO_FAST_BLOCK
+#define JACO_FAST_BLOCK 128
+#endif
+#ifndef JACO_FAST_MINBLOCKS
+#define JACO_FAST_MINBLOCKS 1
+#endif
+#define JACO_LIST_BLOCK 32
+
+__global__ void __launch_bounds__(JACO_FAST_BLOCK, JACO_FAST_MINBLOCKS) jaco_step_fast_kernel(JacoCfg cfg, float* state, int N, int env_offset, const float* action, float* obs, float* reward,
+                                                                    unsigned char* done, unsigned char* succ, float* wb, float* term_obs, int auto_reset, float* gstats,
+                                                                    int* worklist, int* counters) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  float local[16];
+#pragma unroll
+  for (int k = 0; k < 16; k++) local[k] = 0;
+  if (i < N) {
+    float a[JACO_NACT];
+#pragma unroll
+    for (int k = 0; k < JACO_NACT; k++) a[k] = action[(size_t)i * JACO_NACT + k];
+    float r, w; unsigned char d, sc; int needs_reset, why;
+    int rc = entry_step_fast(cfg, state, N, i, env_offset + i, a, obs + (size_t)i * JACO_NOBS, &r, &d, &sc, &w,
+                             term_obs ? term_obs + (size_t)i * JACO_NOBS : nullptr, auto_reset, local, &needs_reset, &why);
+    if (rc == FAST_OK) {
+      reward[i] = r; done[i] = d; succ[i] = sc; wb[i] = w;
+      if (needs_reset) worklist[N + atomicAdd(counters + 1, 1)] = i;
+    } else {
+      worklist[atomicAdd(counters + 0, 1)] = i;
+      int bit = 31 - __clz(why & -why);  // lowest reason bit
+      atomicAdd(counters + 2 + (bit < 0 ? 0 : bit), 1);
+    }
+  }
+  block_stats_flush(local, gstats);
+}
+
+// general path over the bail list, then the general reset over the finished-episode list
+__global__ void __launch_bounds__(JACO_LIST_BLOCK) jaco_step_list_kernel(JacoCfg cfg, float* state, int N, int env_offset, const float* action, float* obs, float* reward,
+                                                                         unsigned char* done, unsigned char* succ, float* wb, float* term_obs, int auto_reset, float* gstats,
+                                                                         const int* worklist, const int* counters) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nb = counters[0], nr = counters[1];
+  if ((int)(blockIdx.x * blockDim.x) >= nb + nr) return;
+  float local[16];
+#pragma unroll
+  for (int k = 0; k < 16; k++) local[k] = 0;
+  if (t < nb) {
+    int i = worklist[t];
+    float a[JACO_NACT];
+#pragma unroll
+    for (int k = 0; k < JACO_NACT; k++) a[k] = action[(size_t)i * JACO_NACT + k];
+    float r, w; unsigned char d, sc;
+    entry_step(cfg, state, N, i, env_offset + i, a, obs + (size_t)i * JACO_NOBS, &r, &d, &sc, &w,
+               term_obs ? term_obs + (size_t)i * JACO_NOBS : nullptr, auto_reset, local);
+    reward[i] = r; done[i] = d; succ[i] = sc; wb[i] = w;
+  } else if (t < nb + nr) {
+    int i = worklist[N + (t - nb)];
+    entry_reset(cfg, state, N, i, env_offset + i, obs + (size_t)i * JACO_NOBS);
   }
   block_stats_flush(local, gstats);
 }
@@ -112,10 +177,16 @@ int jaco_create(const void* model_blob, size_t nbytes, int n_envs, int task_id, 
   JacoModel* m = new JacoModel();
   jaco_model_from_blob((const double*)model_blob, m);
   cudaError_t e = cudaMemcpyToSymbol(c_jaco_model, m, sizeof(JacoModel));
+  const bool fast_ok = fast_model_ok(*m);
   delete m;
   CK(e);
   CK(cudaMalloc(&h->state, sizeof(float) * JACO_NSTATE * (size_t)n_envs));
   CK(cudaMemset(h->state, 0, sizeof(float) * JACO_NSTATE * (size_t)n_envs));
+  h->use_fast = fast_ok ? 1 : 0;
+  if (getenv("JACO_NO_FAST")) h->use_fast = 0;
+  CK(cudaMalloc(&h->worklist, sizeof(int) * 2 * (size_t)n_envs));
+  CK(cudaMalloc(&h->counters, sizeof(int) * 16));
+  CK(cudaMemset(h->counters, 0, sizeof(int) * 16));
   CK(cudaMalloc(&h->stats, sizeof(float) * JACO_NSTATS));
   CK(cudaMemset(h->stats, 0, sizeof(float) * JACO_NSTATS));
   CK(cudaFuncSetAttribute(jaco_step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 0));
@@ -126,11 +197,16 @@ int jaco_create(const void* model_blob, size_t nbytes, int n_envs, int task_id, 
 void jaco_destroy(jaco_handle h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  cudaFree(h->state); cudaFree(h->stats);
+  cudaFree(h->state); cudaFree(h->stats); cudaFree(h->worklist); cudaFree(h->counters);
   cudaFree(h->s_action); cudaFree(h->s_obs); cudaFree(h->s_reward); cudaFree(h->s_wb); cudaFree(h->s_done); cudaFree(h->s_succ);
   delete h;
 }
 const char* jaco_last_error(jaco_handle h) { return h ? h->err : "null handle"; }
+int jaco_debug_counters(jaco_handle h, int* out16) {  /* host copy of the work-list counters (synchronises) */
+  if (!h || !out16) return JACO_EINVAL;
+  CK(cudaMemcpy(out16, h->counters, 16 * sizeof(int), cudaMemcpyDeviceToHost));
+  return JACO_OK;
+}
 int jaco_n_envs(jaco_handle h) { return h ? h->n : 0; }
 long long jaco_launch_count(jaco_handle h) { return h ? h->launches : 0; }
 
@@ -146,8 +222,19 @@ int jaco_reset(jaco_handle h, const uint8_t* mask, float* obs, void* stream) {
 
 int jaco_step(jaco_handle h, const float* action, float* obs, float* reward, uint8_t* done, uint8_t* succ, float* wb, float* term_obs, int auto_reset, void* stream) {
   if (!h || !action || !obs || !reward || !done || !succ || !wb) return JACO_EINVAL;
-  jaco_step_kernel<<<nblocks(h->n), JACO_BLOCK, 0, (cudaStream_t)stream>>>(h->cfg, h->state, h->n, h->env_offset, action, obs, reward, done, succ, wb, term_obs, auto_reset, h->stats);
-  h->launches++;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (h->use_fast) {
+    CK(cudaMemsetAsync(h->counters, 0, 2 * sizeof(int), st));
+    jaco_step_fast_kernel<<<(h->n + JACO_FAST_BLOCK - 1) / JACO_FAST_BLOCK, JACO_FAST_BLOCK, 0, st>>>(h->cfg, h->state, h->n, h->env_offset, action, obs, reward, done, succ, wb,
+                                                                                                   term_obs, auto_reset, h->stats, h->worklist, h->counters);
+    if (!getenv("JACO_FAST_ONLY"))  /* timing experiments only: skips the general pass, results are then incomplete */
+    jaco_step_list_kernel<<<(h->n + JACO_LIST_BLOCK - 1) / JACO_LIST_BLOCK, JACO_LIST_BLOCK, 0, st>>>(h->cfg, h->state, h->n, h->env_offset, action, obs, reward, done, succ, wb,
+                                                                                                   term_obs, auto_reset, h->stats, h->worklist, h->counters);
+    h->launches += 2;
+  } else {
+    jaco_step_kernel<<<nblocks(h->n), JACO_BLOCK, 0, st>>>(h->cfg, h->state, h->n, h->env_offset, action, obs, reward, done, succ, wb, term_obs, auto_reset, h->stats);
+    h->launches++;
+  }
   CK(cudaGetLastError());
   return JACO_OK;
 }

@@ -3,6 +3,7 @@
 // (layout: include/jaco_model_layout.h) and copied once into __constant__ memory.
 #pragma once
 #include <stdint.h>
+#include <math.h>
 #include "../../include/jaco_model_layout.h"
 
 #define JACO_NQ 23
@@ -37,6 +38,7 @@ struct JacoModel {
   float motor_fr[6][2], finger_act[3][5];
   float ee_off[3], ee_obj_off[3], base_pos[3], base_link_pos[3];
   float dof_invw[JACO_NV], meaninertia, hand_sphere[4];
+  float body_sphere[4][4];  // bounding spheres (body frame: centre xyz, radius) of the collision geoms on bodies 6..9
   float dt, gravz;
   JacoGeom geoms[JM_NGEOM];
   JacoPair pairs[JM_NPAIR];
@@ -98,5 +100,30 @@ static inline void jaco_model_from_blob(const double* b, JacoModel* m) {
     S->type = (int)r[0]; S->body = (int)r[1]; S->geom = (int)r[17];
     for (int i = 0; i < 3; i++) { S->pos[i] = (float)r[2 + i]; S->size[i] = (float)r[14 + i]; }
     for (int i = 0; i < 9; i++) S->R[i] = (float)r[5 + i];
+  }
+  // per-body bounding spheres of the hand cluster (hand + three fingers), used by the fast path's proximity tests
+  for (int b = 6; b <= 9; b++) {
+    double c[3] = {0, 0, 0}; int cnt = 0;
+    for (int g = 0; g < JM_NGEOM; g++) if (m->geoms[g].body == b) { for (int i = 0; i < 3; i++) c[i] += m->geoms[g].pos[i]; cnt++; }
+    for (int i = 0; i < 3; i++) c[i] /= (cnt ? cnt : 1);
+    double rad = 0;
+    for (int itn = 0; itn < 400; itn++) {
+      int far = -1; rad = 0;
+      for (int g = 0; g < JM_NGEOM; g++) if (m->geoms[g].body == b) {
+        double d = 0; for (int i = 0; i < 3; i++) d += (m->geoms[g].pos[i] - c[i]) * (m->geoms[g].pos[i] - c[i]);
+        d = sqrt(d) + m->geoms[g].rbound;
+        if (d > rad) { rad = d; far = g; }
+      }
+      if (far < 0) break;
+      double step = 0.5 / (itn + 2);
+      for (int i = 0; i < 3; i++) c[i] += step * (m->geoms[far].pos[i] - c[i]);
+    }
+    rad = 0;
+    for (int g = 0; g < JM_NGEOM; g++) if (m->geoms[g].body == b) {
+      double d = 0; for (int i = 0; i < 3; i++) d += (m->geoms[g].pos[i] - c[i]) * (m->geoms[g].pos[i] - c[i]);
+      d = sqrt(d) + m->geoms[g].rbound; if (d > rad) rad = d;
+    }
+    for (int i = 0; i < 3; i++) m->body_sphere[b - 6][i] = (float)c[i];
+    m->body_sphere[b - 6][3] = (float)(rad * 1.0001 + 1e-6);
   }
 }

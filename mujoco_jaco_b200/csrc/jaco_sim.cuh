@@ -217,6 +217,8 @@ struct JacoSim {
   float accum_rew;
 };
 
+JHD const float* obj_pos(const JacoSim& s) { return s.bx[10]; }  // lagged xpos of the object body
+
 // chain topology helpers
 JHD int ch_parent(int k) { return k < 6 ? k - 1 : 5; }
 JHD bool ch_has_dof(int k, int j) { return k < 6 ? (j <= k) : (j < 6 || j == k); }
@@ -1285,14 +1287,17 @@ JHD void osc_generate(const JacoSim& s, const float* dq, float* u) {
 }
 
 // ------------------------------------------------------------------------------------------- env logic
-JHD float uni(const JacoCfg& cfg, const JacoSim& s, int env_id, int stream, int k) {
+template <class S>
+JHD float uni(const JacoCfg& cfg, const S& s, int env_id, int stream, int k) {
   uint32_t o[4];
   philox4x32(cfg.seed, (uint32_t)(k >> 2), (uint32_t)stream, (uint32_t)env_id, s.rng_counter, o);
   return (float)(o[k & 3] >> 8) * (1.0f / 16777216.0f);
 }
-JHD float uniab(const JacoCfg& cfg, const JacoSim& s, int env_id, int stream, int k, float a, float b) { return a + (b - a) * uni(cfg, s, env_id, stream, k); }
+template <class S>
+JHD float uniab(const JacoCfg& cfg, const S& s, int env_id, int stream, int k, float a, float b) { return a + (b - a) * uni(cfg, s, env_id, stream, k); }
 
-JHD void get_gripper_pose(JacoSim& s) {  // util:309, 667-673
+template <class S>
+JHD void get_gripper_pose(S& s) {  // util:309, 667-673
   v3copy(s.gripper_pose, s.eepos);
   quat_to_euler_rxyz(s.gripper_pose + 3, s.eeq);
 }
@@ -1309,13 +1314,14 @@ JHD int get_touch(const JacoSim& s) {  // util:470-490
   if (outer) return 2;
   return 0;
 }
-JHD void rulebased_subgoal(const JacoCfg& cfg, JacoSim& s, int env_id, float* pos, float* ori) {  // util:273-300
+template <class S>
+JHD void rulebased_subgoal(const JacoCfg& cfg, S& s, int env_id, float* pos, float* ori) {  // util:273-300
   if (cfg.task == JACO_TASK_PLACING) { v3copy(pos, s.dest_goal); ori[0] = 0; ori[1] = JPI / 2; ori[2] = 0; return; }
   float D[3], n;
   v3sub(D, s.gripper_pose, s.obj_goal); n = v3norm(D);
   for (int i = 0; i < 3; i++) pos[i] = D[i] / n * 0.12f + s.obj_goal[i] + (uni(cfg, s, env_id, 1, i) - 0.5f) / 25;
   if (pos[2] < 0.1898f + 0.1f) pos[2] = 0.1898f + 0.1f;
-  if (pos[1] > s.bx[10][1] - 0.15f) pos[1] = s.bx[10][1] - 0.15f;
+  if (pos[1] > obj_pos(s)[1] - 0.15f) pos[1] = obj_pos(s)[1] - 0.15f;
   float x = -D[0] / n, y = -D[1] / n, z = -D[2] / n;
   float qp = sqrtf(2.0f) / 2, qv[4] = {qp, qp * x, qp * y, qp * z}, qd[4] = {sqrtf(3.0f) / 2, 0.5f * x, 0.5f * y, 0.5f * z}, rv[3], rd[3], rr[3];
   quat_to_euler_rxyz(rv, qv); quat_to_euler_rxyz(rd, qd);
@@ -1323,7 +1329,8 @@ JHD void rulebased_subgoal(const JacoCfg& cfg, JacoSim& s, int env_id, float* po
   rr[0] -= JPI / 2;
   for (int i = 0; i < 3; i++) ori[i] = rr[i] + (uni(cfg, s, env_id, 1, 3 + i) - 0.5f) / 10;
 }
-JHD void get_observation(const JacoCfg& cfg, JacoSim& s, int env_id, float* o) {  // util:223-271
+template <class S>
+JHD void get_observation(const JacoCfg& cfg, S& s, int env_id, float* o) {  // util:223-271
   get_gripper_pose(s);
   s.touch_index = get_touch(s);
   float sp[3], so[3], base[3] = {0, 0, 0};
@@ -1331,13 +1338,14 @@ JHD void get_observation(const JacoCfg& cfg, JacoSim& s, int env_id, float* o) {
   o[0] = (float)s.touch_index;
   for (int i = 0; i < 3; i++) { o[1 + i] = s.gripper_pose[i] - base[i]; o[4 + i] = s.gripper_pose[3 + i] / JPI; }
   o[7] = (s.grip - 0.8f) / 0.2f;
-  for (int i = 0; i < 3; i++) { o[8 + i] = s.bx[10][i] - base[i]; o[11 + i] = 0; o[14 + i] = s.dest_goal[i] - ((cfg.variant != 0 && cfg.obs_mode != 0) ? base[i] : 0.0f); }
+  for (int i = 0; i < 3; i++) { o[8 + i] = obj_pos(s)[i] - base[i]; o[11 + i] = 0; o[14 + i] = s.dest_goal[i] - ((cfg.variant != 0 && cfg.obs_mode != 0) ? base[i] : 0.0f); }
   if (cfg.obs_mode == 1) { rulebased_subgoal(cfg, s, env_id, sp, so); for (int i = 0; i < 3; i++) { o[17 + i] = sp[i] - base[i]; o[20 + i] = so[i] / JPI; } }
   else if (cfg.obs_mode == 2) { for (int i = 0; i < 3; i++) { o[17 + i] = s.gripper_pose[i]; o[20 + i] = s.gripper_pose[3 + i] / JPI; } }
   else { for (int i = 0; i < 3; i++) { o[17 + i] = s.reach_goal[i] - base[i]; o[20 + i] = s.reach_goal[3 + i] / JPI; } }
   o[23] = 0; o[24] = JPI / 2; o[25] = 0;
 }
-JHD float reach_ang_diff(const JacoSim& s) {  // util:323-333
+template <class S>
+JHD float reach_ang_diff(const S& s) {  // util:323-333
   float g[4], t[4], ge[3], te[3], d[3];
   euler_rxyz_to_quat(g, s.gripper_pose[3], s.gripper_pose[4], s.gripper_pose[5]);
   euler_rxyz_to_quat(t, s.reach_goal[3], s.reach_goal[4], s.reach_goal[5]);
@@ -1347,7 +1355,8 @@ JHD float reach_ang_diff(const JacoSim& s) {  // util:323-333
   if (a > JPI) a = 2 * JPI - a;
   return a;
 }
-JHD float get_reward(const JacoCfg& cfg, const JacoSim& s) {  // util:312-446
+template <class S>
+JHD float get_reward(const JacoCfg& cfg, const S& s) {  // util:312-446
   if (cfg.task == JACO_TASK_REACHING) {
     float d[3]; v3sub(d, s.gripper_pose, s.reach_goal);
     float dist = v3norm(d), ang = reach_ang_diff(s);
@@ -1362,7 +1371,7 @@ JHD float get_reward(const JacoCfg& cfg, const JacoSim& s) {  // util:312-446
     float scale = cfg.task == JACO_TASK_GRASPING ? 0.05f : 0.01f;
     float ev[3], down[3] = {0, 0, -1}, up[3] = {0, 0, 1}, xyz[3], tv[3], dv[3];
     get_rotation(ev, s.gripper_pose[3], s.gripper_pose[4], s.gripper_pose[5], down, 0);
-    v3sub(xyz, s.bx[10], s.gripper_pose);
+    v3sub(xyz, obj_pos(s), s.gripper_pose);
     float od = v3norm(xyz), x = xyz[0] / od, z = xyz[2] / od;
     // fp32 guard: |x| / sqrt(1 - z^2) can round past 1 when the object sits in the gripper's x-z plane (DESIGN.md "deviations")
     float pitch = -acosf(fminf(fmaxf(z, -1.0f), 1.0f)), yaw = -acosf(fminf(fmaxf(-x / sqrtf(fmaxf(1 - z * z, 1e-30f)), -1.0f), 1.0f));
@@ -1374,16 +1383,17 @@ JHD float get_reward(const JacoCfg& cfg, const JacoSim& s) {  // util:312-446
     if (s.touch_index == 1) r += 5 * 0.5f * 0.3f;
     else if (s.touch_index == 2) r -= 5 * 0.5f * 0.3f;
     else if (s.touch_index == 3) r += 5 * 0.5f;
-    r += 100 * (s.bx[10][2] - 0.1898f);
+    r += 100 * (obj_pos(s)[2] - 0.1898f);
     return r * scale;
   }
   return 0;
 }
-JHD int terminal_inspection(const JacoCfg& cfg, JacoSim& s, float* bonus, float* wb, int* succ) {  // util:492-600
+template <class S>
+JHD int terminal_inspection(const JacoCfg& cfg, S& s, float* bonus, float* wb, int* succ) {  // util:492-600
   s.num_episodes += 1;
   float d[3]; *succ = 0; *bonus = 0;
   v3sub(d, s.eepos, MDL.base_pos); *wb = v3norm(d);
-  const float* op = s.bx[10];
+  const float* op = obj_pos(s);
   float dx = s.dest_goal[0] - op[0], dy = s.dest_goal[1] - op[1], dest_diff = sqrtf(dx * dx + dy * dy);
   float q2 = s.qpos[2];
   if (JPI - 0.1f < q2 && q2 < JPI + 0.1f) { *bonus = -1; return 1; }
@@ -1418,7 +1428,8 @@ JHD int terminal_inspection(const JacoCfg& cfg, JacoSim& s, float* bonus, float*
   return 0;
 }
 // gripper command of substep i (numpy.linspace(prev, new, 50), util:631)
-JHD float ramp_value(const JacoSim& s, int i) {
+template <class S>
+JHD float ramp_value(const S& s, int i) {
   if (!s.action_in) return s.grip;
   if (i >= 49) return s.ramp1;
   return s.ramp0 + i * ((s.ramp1 - s.ramp0) / 49);
@@ -1431,7 +1442,8 @@ JHD void substep(JacoSim& s, const float* u, int i, bool want_touch) {
   mj_forward(s, want_touch);
   mj_euler(s);
 }
-JHD void take_action(JacoSim& s, const float* a) {  // util:602-646
+template <class S>
+JHD void take_action(S& s, const float* a) {  // util:602-646
   s.action_in = 1;
   get_gripper_pose(s);
   for (int i = 0; i < 3; i++) { s.target[i] = s.gripper_pose[i] + a[i] / 25; s.target[3 + i] = s.gripper_pose[3 + i] + a[3 + i] / 5; }

@@ -133,6 +133,12 @@ class JacoVecEnv:
         self._check(self.L.jaco_stats(self.h, _ptr(self._stats), int(clear), self._stream()))
         return self._stats
 
+    def debug_counters(self):
+        """Host copy of the step work-list counters: [n_bail, n_reset (last step), bail-reason histogram...]."""
+        out = np.zeros(16, np.int32)
+        self._check(self.L.jaco_debug_counters(self.h, out.ctypes.data_as(C.c_void_p)))
+        return out
+
     def launch_count(self):
         return int(self.L.jaco_launch_count(self.h))
 

@@ -3,7 +3,7 @@
 // without a GPU.  Never loaded by the product; the shipped library only launches the CUDA kernels.
 #include <string.h>
 #define JACO_COLLISION_STATS 1
-#include "../../mujoco_jaco_b200/csrc/jaco_sim.cuh"
+#include "../../mujoco_jaco_b200/csrc/jaco_fast.cuh"
 
 extern "C" {
 void hh_init(const double* blob) { jaco_model_from_blob(blob, &g_jaco_model_host); }
@@ -63,3 +63,26 @@ extern "C" void hh_step_trace(int task, int variant, unsigned long long seed, in
 }
 
 extern "C" void hh_cstats(long long* out, int clear) { for (int i = 0; i < 16; i++) { out[i] = g_cstats[i]; if (clear) g_cstats[i] = 0; } }
+
+// fast path (jaco_fast.cuh) with the same fall-back protocol as the CUDA launcher: bail -> general path from the
+// untouched pre-step state; finished episodes are re-initialised by the general reset.  why[i] = bail reason bits.
+extern "C" void hh_step_fast(int task, int variant, unsigned long long seed, int env_offset, float* state, int N, const float* action, float* obs,
+             float* reward, unsigned char* done, unsigned char* succ, float* wb, int auto_reset, float* stats16, int* why, int allow_fallback) {
+  JacoCfg c = mkcfg(task, variant, seed);
+  for (int i = 0; i < N; i++) {
+    int nr = 0; why[i] = 0;
+    int rc = entry_step_fast(c, state, N, i, env_offset + i, action + (size_t)i * 7, obs + (size_t)i * JACO_NOBS, reward + i, done + i, succ + i, wb + i, 0, auto_reset, stats16, &nr, why + i);
+    if (rc == FAST_OK) { if (nr) entry_reset(c, state, N, i, env_offset + i, obs + (size_t)i * JACO_NOBS); }
+    else if (allow_fallback) entry_step(c, state, N, i, env_offset + i, action + (size_t)i * 7, obs + (size_t)i * JACO_NOBS, reward + i, done + i, succ + i, wb + i, 0, auto_reset, stats16);
+  }
+}
+extern "C" int hh_fast_model_ok() { return fast_model_ok(g_jaco_model_host) ? 1 : 0; }
+// chain pass probe: M (9x9 dense), bias9, J 6x6, eepos, eeq at (q9, v9) with reference point O
+extern "C" void hh_fast_chain(const float* q9, const float* v9, const float* O, float* M81, float* bias9, float* J36, float* eepos, float* eeq) {
+  ChainOut c; fast_chain<true>(q9, v9, O, nullptr, c);
+  for (int i = 0; i < 81; i++) M81[i] = 0;
+  for (int i = 0; i < 6; i++) for (int j = 0; j <= i; j++) M81[9 * i + j] = M81[9 * j + i] = c.A[PK(i, j)];
+  for (int f = 0; f < 3; f++) { M81[9 * (6 + f) + 6 + f] = c.Dg[f]; for (int j = 0; j < 6; j++) M81[9 * (6 + f) + j] = M81[9 * j + 6 + f] = c.B[f][j]; }
+  memcpy(bias9, c.bias, 36); memcpy(J36, c.J, 144); memcpy(eepos, c.eepos, 12); memcpy(eeq, c.eeq, 16);
+}
+extern "C" void hh_body_spheres(float* out16) { memcpy(out16, g_jaco_model_host.body_sphere, 64); }
