@@ -7,13 +7,17 @@ import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 REPO = os.path.dirname(HERE)
-SO_PATH = os.path.join(HERE, "libjaco_b200.so")
-SOURCES = [os.path.join(HERE, "csrc", f) for f in ("jaco_kernels.cu", "jaco_sim.cuh", "jaco_fast.cuh", "jaco_model.h")] + [
+SO_PATH = os.environ.get("JACO_B200_LIB") or os.path.join(HERE, "libjaco_b200.so")  # override: diagnostic builds only
+CSRC = os.path.join(HERE, "csrc")
+UNITS = ["jaco_kernels.cu", "jaco_kernel_fast.cu", "jaco_kernel_coop.cu"]   # compiled in parallel, linked into one .so
+HEADERS = [os.path.join(CSRC, f) for f in ("jaco_sim.cuh", "jaco_fast.cuh", "jaco_coop.cuh", "jaco_launch.h", "jaco_model.h")] + [
     os.path.join(REPO, "include", "jaco_b200.h"), os.path.join(REPO, "include", "jaco_model_layout.h")]
-NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-shared", "-Xcompiler", "-fPIC"]
+SOURCES = [os.path.join(CSRC, u) for u in UNITS] + HEADERS
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-Xcompiler", "-fPIC"]
 
 SYMBOLS = ["jaco_create", "jaco_destroy", "jaco_last_error", "jaco_reset", "jaco_step", "jaco_step_host",
-           "jaco_get_state", "jaco_set_state", "jaco_debug_substep", "jaco_stats", "jaco_debug_counters", "jaco_n_envs", "jaco_launch_count", "jaco_fp32_peak_tflops"]
+           "jaco_get_state", "jaco_set_state", "jaco_debug_substep", "jaco_stats", "jaco_debug_counters", "jaco_n_envs",
+           "jaco_launch_count", "jaco_fp32_peak_tflops"]
 
 
 def needs_build():
@@ -23,14 +27,30 @@ def needs_build():
     return any(os.path.exists(s) and os.path.getmtime(s) > t for s in SOURCES)
 
 
-def build(force=False, verbose=False):
-    """Compile the CUDA extension in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
-    if not force and not needs_build():
-        return SO_PATH
+def build(force=False, verbose=False, defines=(), out=None):
+    """Compile the CUDA extension in-tree for sm_100a (nvcc cross-compiles without a GPU).  Each unit is compiled
+    only when it (or a header) is newer than its object file; the units build in parallel."""
+    out = out or SO_PATH
+    if not force and out == SO_PATH and not needs_build():
+        return out
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", SO_PATH, SOURCES[0]]
-    subprocess.check_call(cmd)
-    return SO_PATH
+    tag = "".join("_" + d.replace("=", "") for d in defines)
+    objdir = os.path.join(HERE, "build" + tag)
+    os.makedirs(objdir, exist_ok=True)
+    hdr_t = max(os.path.getmtime(h) for h in HEADERS)
+    procs, objs = [], []
+    for u in UNITS:
+        src, obj = os.path.join(CSRC, u), os.path.join(objdir, u[:-3] + ".o")
+        objs.append(obj)
+        if not force and os.path.exists(obj) and os.path.getmtime(obj) > max(hdr_t, os.path.getmtime(src)):
+            continue
+        cmd = [nvcc] + NVCC_FLAGS + ["-D" + d for d in defines] + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", obj, src]
+        procs.append((u, subprocess.Popen(cmd)))
+    for u, pr in procs:
+        if pr.wait() != 0:
+            raise RuntimeError(f"nvcc failed on {u}")
+    subprocess.check_call([nvcc, "-shared", "-o", out] + objs)
+    return out
 
 
 _lib = None

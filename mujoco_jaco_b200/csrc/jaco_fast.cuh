@@ -9,9 +9,10 @@
 // A thread that leaves the regime returns FAST_BAIL *without touching the state*; the host side then advances
 // that environment with the general path (jaco_sim.cuh) from the same pre-step state, so results never depend
 // on which path ran beyond fp32 rounding.  Everything here is __host__ __device__ so tests/harness can run the
-// identical source on the CPU against the oracle.
+// identical source on the CPU in the parity tests.
 #pragma once
 #include "jaco_sim.cuh"
+#include "jaco_coop.cuh"
 
 #define FAST_OK 0
 #define FAST_BAIL 1
@@ -32,9 +33,10 @@ struct FastSim {
   uint32_t rng_counter;
   float obj_goal[3], dest_goal[3], reach_goal[6], gripper_pose[6];
   float lagq[9], lagv[9], accum_rew;
+  int touch_now;              // touch class of the last forward (set by the cooperative path; 0 without arm contact)
 };
 JHD const float* obj_pos(const FastSim& s) { return s.objp; }
-JHD int get_touch(const FastSim&) { return 0; }  // the fast regime has no arm contact => all 20 sensors read 0
+JHD int get_touch(const FastSim& s) { return s.touch_now; }  // 0 unless the cooperative path found pad contacts
 
 // ------------------------------------------------------------------------------------------- chain pass
 // Outputs of one pass of the chain dynamics at (q, v): inertia blocks, bias, EE Jacobian / pose.
@@ -46,6 +48,7 @@ struct ChainOut {
   float J[6][6];      // EE Jacobian (rows: lin xyz, ang xyz; columns: arm joints)
   float eepos[3], eeq[4];
   int near;           // BAIL_* bits of the proximity tests that could not prove "no arm contact"
+  float bp[7][3], bRm[7][9];  // world pose of bodies 3..9 (the bodies that carry collision geoms); consumed only by the cooperative path
 };
 struct SceneBoxes {   // world pose of the three scene boxes the arm can touch (geoms 1 holder, 2 object, 3 dest)
   float hp[3], hR[9], hh[3];
@@ -53,13 +56,6 @@ struct SceneBoxes {   // world pose of the three scene boxes the arm can touch (
   float dp[3], dR[9], dh[3];
 };
 
-// squared distance from point c to an oriented box (centre bp, rows of bR = world-from-box, half sizes h)
-JHD float point_box_dist2(const float* c, const float* bp, const float* bR, const float* h) {
-  float d[3], l[3];
-  v3sub(d, c, bp); m3tmulv(l, bR, d);
-  float e0 = fmaxf(fabsf(l[0]) - h[0], 0.0f), e1 = fmaxf(fabsf(l[1]) - h[1], 0.0f), e2 = fmaxf(fabsf(l[2]) - h[2], 0.0f);
-  return e0 * e0 + e1 * e1 + e2 * e2;
-}
 JHD bool sphere_clear_of_box(const float* c, float r, const float* bp, const float* bR, const float* h) {
   float rr = r + FAST_CLEAR_EPS;
   return point_box_dist2(c, bp, bR, h) > rr * rr;
@@ -162,6 +158,11 @@ JHD void fast_chain(const float* q, const float* v, const float* O, const SceneB
       chain_body(k + 1, R, p, Sa[k], v[k], O, w, vl, aa, al, Sl[k], Ih[k], II[k], Fa[k], Fl[k]);
       Im[k] = m.mass[k + 1];
       if (sb && k >= 2 && k <= 4) { if (!capsule_clear(28 + k, R, p, *sb)) o.near |= BAIL_FOREARM; }  // geoms 30,31,32 on bodies 3,4,5
+      if (sb && k >= 2) {
+        v3copy(o.bp[k - 2], p);
+#pragma unroll
+        for (int i = 0; i < 9; i++) o.bRm[k - 2][i] = R[i];
+      }
     }
 #pragma unroll
     for (int i = 0; i < 4; i++) Qp[i] = qn[i];
@@ -194,6 +195,11 @@ JHD void fast_chain(const float* q, const float* v, const float* O, const SceneB
     v3copy(wf, w); v3copy(vf, vl); v3copy(af, aa); v3copy(lf, al);
     m3mulv(t, Rp, m.ch_pos[k]); v3add(p, pp, t);
     chain_joint(k, Qp, q[k], qn, R);
+    if (sb) {
+      v3copy(o.bp[4 + f], p);
+#pragma unroll
+      for (int i = 0; i < 9; i++) o.bRm[4 + f][i] = R[i];
+    }
     if (fine && !body_sphere_clear(1 + f, R, p, *sb)) o.near |= BAIL_HAND;
     m3mulv(a, R, m.ch_axis[k]);
     chain_body(k + 1, R, p, a, v[k], O, wf, vf, af, lf, s, h, IO, fa, fl);
@@ -273,7 +279,7 @@ JHD int chain_solve(const ChainOut& c, float hdt, const float* r, float* x) {
 // abr_control OSC.generate on the quantities of one forward, without explicit inverses:
 // A = L L^T, Y = L^-1 J^T, Mx_inv = Y^T Y, Mx u_task by a second Cholesky.  Returns 0 when the reference would
 // take the pinv branch (|det Mx_inv| < 1e-3) or a pivot fails -- the caller bails to the general path.
-JHD int fast_osc(const ChainOut& c, const float* tq, const float* target, const float* dq, float* u) {
+JHD int fast_osc(const ChainOut& c, const float* tq, const float* target, const float* dq, float* u, bool allow_pinv = false) {
   const float kp = 50, ko = 180, kv = 20, vmax0 = 0.4f, vmax1 = 1.0472f;
   float L[21], Y[6][6], X[21];
 #pragma unroll
@@ -303,7 +309,8 @@ JHD int fast_osc(const ChainOut& c, const float* tq, const float* target, const 
   float det = 1;
 #pragma unroll
   for (int i = 0; i < 6; i++) det *= X[PK(i, i)] * X[PK(i, i)];
-  if (!ok || !(fabsf(det) >= 1e-3f)) return 0;
+  const bool singular = !ok || !(fabsf(det) >= 1e-3f);
+  if (singular && !allow_pinv) return 0;
   float ut[6];
 #pragma unroll
   for (int i = 0; i < 3; i++) ut[i] = c.eepos[i] - target[i];
@@ -316,7 +323,14 @@ JHD int fast_osc(const ChainOut& c, const float* tq, const float* target, const 
   if (na > sat_abg) { float r = sat_abg / na; sc[3] *= r; sc[4] *= r; sc[5] *= r; }
 #pragma unroll
   for (int i = 0; i < 6; i++) ut[i] = kv * sc[i] * ((i < 3 ? kp : ko) / kv) * ut[i];
-  chol_solve_packed<6>(X, ut);  // ut <- Mx u_task
+  if (!singular) chol_solve_packed<6>(X, ut);  // ut <- Mx u_task
+  else {  // numpy.linalg.pinv(Mx_inv, rcond = 1e-4) branch of the reference controller (rare)
+    float Xf[36], Mx[36], f[6];
+    for (int i = 0; i < 6; i++) for (int j = 0; j < 6; j++) { float sm = 0; for (int k = 0; k < 6; k++) sm += Y[k][i] * Y[k][j]; Xf[6 * i + j] = sm; }
+    sym_pinv6(Xf, 1e-4f, Mx);
+    for (int i = 0; i < 6; i++) { float sm = 0; for (int j = 0; j < 6; j++) sm += Mx[6 * i + j] * ut[j]; f[i] = sm; }
+    for (int i = 0; i < 6; i++) ut[i] = f[i];
+  }
 #pragma unroll
   for (int i = 0; i < 6; i++) {
     float sm = 0, tt = 0;
@@ -782,9 +796,96 @@ static inline bool fast_model_ok(const JacoModel& m) {
   return true;
 }
 
+// Owner thread -> warp workspace, stage A: poses of the geom-carrying bodies only (cheap; no kinematics redone)
+JHD void coop_publish_poses(CoopWS& w, const ChainOut& c, const FreeBody& fo, const FreeBody& fd, int flags) {
+  v3set(w.bx[0], 0, 0, 0);
+  { const float I[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}; for (int i = 0; i < 9; i++) w.bR[0][i] = I[i]; }
+  for (int b = 3; b <= 9; b++) { v3copy(w.bx[b], c.bp[b - 3]); for (int i = 0; i < 9; i++) w.bR[b][i] = c.bRm[b - 3][i]; }
+  v3copy(w.bx[10], fo.x); v3copy(w.bx[11], fd.x);
+  for (int i = 0; i < 9; i++) { w.bR[10][i] = fo.R[i]; w.bR[11][i] = fd.R[i]; }
+  w.flags = flags;
+}
+// Owner thread -> warp workspace: the mj_forward quantities of this substep the cooperative path consumes.
+JHD void coop_publish(CoopWS& w, const FastSim& s, const ChainOut& c, const FreeBody& fo, const FreeBody& fd, const float* fsm9, int want_touch) {
+  const JacoModel& m = MDL;
+  v3set(w.bx[0], 0, 0, 0); v3set(w.bw[0], 0, 0, 0); v3set(w.bv[0], 0, 0, 0);
+  { const float I[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}; for (int i = 0; i < 9; i++) w.bR[0][i] = I[i]; }
+  float Q6[4] = {1, 0, 0, 0};
+  {  // chain kinematics + body velocities (mj_kinematics, mj_comVel restricted to what the rows need)
+    float Qp[4] = {1, 0, 0, 0};
+    for (int k = 0; k < 9; k++) {
+      const int pb = ch_parent(k) + 1, b = k + 1;
+      float t[3], qn[4], r[3];
+      m3mulv(t, w.bR[pb], m.ch_pos[k]); v3add(w.bx[b], w.bx[pb], t);
+      chain_joint(k, k <= 5 ? Qp : Q6, s.qpos[k], qn, w.bR[b]);
+      m3mulv(w.ax[k], w.bR[b], m.ch_axis[k]);
+      v3sub(r, w.bx[b], w.bx[pb]); v3cross(t, w.bw[pb], r); v3add(w.bv[b], w.bv[pb], t);
+      v3addscl(w.bw[b], w.bw[pb], w.ax[k], s.qvel[k]);
+      if (k <= 5) for (int i = 0; i < 4; i++) Qp[i] = qn[i];
+      if (k == 5) for (int i = 0; i < 4; i++) Q6[i] = qn[i];
+    }
+  }
+  for (int f = 0; f < 2; f++) {
+    const FreeBody& fb = f ? fd : fo; const int b = 10 + f, d = 9 + 6 * f;
+    v3copy(w.bx[b], fb.x);
+    for (int i = 0; i < 9; i++) w.bR[b][i] = fb.R[i];
+    v3copy(w.bv[b], s.qvel + d); m3mulv(w.bw[b], fb.R, s.qvel + d + 3);
+    for (int i = 0; i < 21; i++) w.Mf[f][i] = fb.M[i];
+    float y[6];
+    for (int i = 0; i < 6; i++) y[i] = -fb.bias[i];
+    chol_solve_packed<6>(fb.L, y);
+    for (int i = 0; i < 6; i++) w.asm_[d + i] = y[i];
+  }
+  for (int i = 0; i < 9; i++) w.qpos9[i] = s.qpos[i];
+  for (int i = 0; i < JACO_NV; i++) { w.qvel[i] = s.qvel[i]; w.warm[i] = s.warm[i]; }
+  for (int i = 0; i < 45; i++) w.Mc[i] = 0;
+  for (int i = 0; i < 21; i++) w.Mc[i] = c.A[i];
+  for (int f = 0; f < 3; f++) { for (int j = 0; j < 6; j++) w.Mc[PK(6 + f, j)] = c.B[f][j]; w.Mc[PK(6 + f, 6 + f)] = c.Dg[f]; }
+  { float a9[9]; chain_solve(c, 0.0f, fsm9, a9); for (int i = 0; i < 9; i++) w.asm_[i] = a9[i]; }
+  w.want_touch = want_touch;
+}
+
+JHD int touch_class(const float* touch) {  // env_mujoco_util.py:470-490 on the 20 sensor readings
+  const float th = 0.001f;
+  int thumb = 0, index = 0, pinky = 0, inner = 0, outer = 0;
+  for (int i = 1; i < 5; i++) if (touch[i] > th) thumb = 1;
+  for (int i = 5; i < 9; i++) if (touch[i] > th) index = 1;
+  for (int i = 9; i < 13; i++) if (touch[i] > th) pinky = 1;
+  for (int i = 0; i < 13; i++) if (touch[i] > th) inner = 1;
+  for (int i = 13; i < 20; i++) if (touch[i] > th) outer = 1;
+  if ((thumb && index) || (thumb && pinky)) return 3;
+  if (inner) return 1;
+  if (outer) return 2;
+  return 0;
+}
+// Euler step of one free box given the solved acceleration (warm start) and constraint force
+JHD void free_integrate(const FreeBody& fb, const float* a6, const float* fcon6, float* q7, float* v6, float* warm6) {
+  const float h = MDL.dt;
+  float y[6];
+#pragma unroll
+  for (int i = 0; i < 6; i++) { warm6[i] = a6[i]; y[i] = -fb.bias[i] + fcon6[i]; }
+  chol_solve_packed<6>(fb.L, y);
+#pragma unroll
+  for (int i = 0; i < 6; i++) v6[i] += h * y[i];
+  q7[0] += h * v6[0]; q7[1] += h * v6[1]; q7[2] += h * v6[2];
+  float n = sqrtf(v6[3] * v6[3] + v6[4] * v6[4] + v6[5] * v6[5]);
+  if (n > JMINVAL) {
+    float sh, chh; sincosf(0.5f * n * h, &sh, &chh);
+    float inv = sh / n, dq[4] = {chh, v6[3] * inv, v6[4] * inv, v6[5] * inv}, rq[4];
+    quat_mul(rq, q7 + 3, dq);
+    q7[3] = rq[0]; q7[4] = rq[1]; q7[5] = rq[2]; q7[6] = rq[3];
+    quat_normalize(q7 + 3);
+  }
+}
+
 // One env step on the fast path.  Returns FAST_OK with all outputs written into s / obs / ..., or FAST_BAIL
 // (reason bits in *why) with s in an unspecified state -- the caller must not store it.
-JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* action, float* obs, float* reward, int* done, int* succ, float* wb, int* why) {
+// COOP = true: nothing bails for contact reasons; environments that need the general contact handling get it from
+// the warp-cooperative path (jaco_coop.cuh) through the per-warp workspace ws, substep by substep.  All lanes of a
+// warp must then call this function together (lanes without an environment pass active = false).
+template <bool COOP>
+JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* action, float* obs, float* reward, int* done, int* succ, float* wb, int* why,
+                      CoopWS* ws = nullptr, bool active = true) {
   const JacoModel& m = MDL;
   const float h = m.dt;
   ChainOut c;
@@ -806,7 +907,9 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
   if (cfg.task == JACO_TASK_REACHING) { s.grip = 0.6f; s.ramp0 = s.ramp1 = 0.6f; }
   euler_rxyz_to_quat(s.tq, s.target[3], s.target[4], s.target[5]);
   quat_normalize(s.tq);
-  if (!fast_osc(c, s.tq, s.target, s.qvel, s.u)) { *why = BAIL_OSC; return FAST_BAIL; }
+  s.touch_now = 0;
+  int dead = 0;  // COOP: bail reason latched, the thread keeps pace with its warp until the step ends
+  if (!fast_osc(c, s.tq, s.target, s.qvel, s.u, COOP)) { *why = BAIL_OSC; if (!COOP) return FAST_BAIL; dead |= BAIL_OSC; }
   // static holder box
   SceneBoxes sb;
   { const JacoGeom& G = m.geoms[FG_HOLDER];
@@ -851,7 +954,7 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
     float O[3]; v3copy(O, s.eepos);
     fast_chain<true>(s.qpos, s.qvel, O, &sb, c);
     bail |= c.near;
-    if (bail) { *why = bail; return FAST_BAIL; }
+    if (!COOP && bail) { *why = bail; return FAST_BAIL; }
     // ---- actuation + smooth forces of the chain (fwd_actuation, mj_passive)
     float fsm[9], acc[9];
     const float gcmd = ramp_value(s, it);
@@ -864,24 +967,71 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
       float f = A[0] * cc - A[0] * s.qpos[6 + i];
       fsm[6 + i] = fminf(fmaxf(f, A[3]), A[4]) - c.bias[6 + i] - m.ch_damping[6 + i] * s.qvel[6 + i];
     }
-    if (it == 49) {  // what the next env step (either path) needs from this forward
-      chain_solve(c, 0.0f, fsm, acc);
+    // ---- general contact handling on demand (warp-cooperative)
+    int solved = 0;   // bit mask of the blocks (1 chain, 2 object, 4 dest) the cooperative path solved for this env
+    float qacc_g[JACO_NV], fcon_g[JACO_NV];
+    if (COOP) {
+      const bool need = active && !dead && bail != 0;
+      const int flags = ((bail & (BAIL_OBJ | BAIL_DEST)) ? 0 : COOP_SIMPLE_OBJ) | ((bail & (BAIL_LIMIT | BAIL_OBJ | BAIL_DEST)) ? COOP_FORCE_B : 0);
+#ifdef __CUDA_ARCH__
+      unsigned pending = __ballot_sync(0xffffffffu, need);
+      const int mylane = threadIdx.x & 31;
+      while (pending) {
+        const int L = __ffs(pending) - 1; pending &= pending - 1;
+        JPROF_T(t0);
+        if (mylane == L) coop_publish_poses(*ws, c, fo, fd, flags);
+        __syncwarp();
+        const int goB = coop_stageA(*ws);
+        JPROF_T(t1);
+        JPROF_ADD(0, 1); JPROF_ADD(1, t1 - t0);
+        if (!goB) continue;
+        if (mylane == L) coop_publish(*ws, s, c, fo, fd, fsm, it == 49);
+        __syncwarp();
+        JPROF_T(t2);
+        const int sv = coop_stageB(*ws);
+        __syncwarp();
+        JPROF_T(t3);
+        JPROF_ADD(8, 1); JPROF_ADD(9, t2 - t1); JPROF_ADD(2, t3 - t2); if (sv) JPROF_ADD(3, 1);
+        if (mylane == L) {
+          solved = sv;
+          if (sv) { for (int i = 0; i < JACO_NV; i++) { qacc_g[i] = ws->qacc[i]; fcon_g[i] = ws->fcon[i]; } if (it == 49) s.touch_now = touch_class(ws->touch); }
+        }
+        __syncwarp();
+      }
+#else
+      if (need) {
+        coop_publish_poses(*ws, c, fo, fd, flags);
+        if (coop_stageA(*ws)) {
+          coop_publish(*ws, s, c, fo, fd, fsm, it == 49);
+          solved = coop_stageB(*ws);
+          if (solved) { for (int i = 0; i < JACO_NV; i++) { qacc_g[i] = ws->qacc[i]; fcon_g[i] = ws->fcon[i]; } if (it == 49) s.touch_now = touch_class(ws->touch); }
+        }
+      }
+#endif
+    }
+    if (it == 49) {  // what the next env step needs from this forward
+      if (solved & 1) { for (int i = 0; i < 9; i++) s.warm[i] = qacc_g[i]; }
+      else { chain_solve(c, 0.0f, fsm, acc); for (int i = 0; i < 9; i++) s.warm[i] = acc[i]; }
 #pragma unroll
-      for (int i = 0; i < 9; i++) { s.warm[i] = acc[i]; s.lagq[i] = s.qpos[i]; s.lagv[i] = s.qvel[i]; }
+      for (int i = 0; i < 9; i++) { s.lagq[i] = s.qpos[i]; s.lagv[i] = s.qvel[i]; }
     }
     // ---- mj_Euler, chain (implicit joint damping)
-    if (!chain_solve(c, h, fsm, acc)) { *why = BAIL_NAN; return FAST_BAIL; }
+    if (solved & 1) { for (int i = 0; i < 9; i++) fsm[i] += fcon_g[i]; }
+    if (!chain_solve(c, h, fsm, acc)) { *why = BAIL_NAN; if (!COOP) return FAST_BAIL; dead |= BAIL_NAN; }
 #pragma unroll
     for (int i = 0; i < 9; i++) { s.qvel[i] += h * acc[i]; s.qpos[i] += h * s.qvel[i]; }
     // ---- free boxes: contact solve + Euler
-    fast_free_step(fo, co, s.qpos + 9, s.qvel + 9, s.warm + 9);
-    fast_free_step(fd, cd, s.qpos + 16, s.qvel + 15, s.warm + 15);
+    if (solved & 2) free_integrate(fo, qacc_g + 9, fcon_g + 9, s.qpos + 9, s.qvel + 9, s.warm + 9);
+    else fast_free_step(fo, co, s.qpos + 9, s.qvel + 9, s.warm + 9);
+    if (solved & 4) free_integrate(fd, qacc_g + 15, fcon_g + 15, s.qpos + 16, s.qvel + 15, s.warm + 15);
+    else fast_free_step(fd, cd, s.qpos + 16, s.qvel + 15, s.warm + 15);
     // ---- controller output for the next substep from this forward's mjData and the fresh joint velocity
     v3copy(s.eepos, c.eepos);
 #pragma unroll
     for (int i = 0; i < 4; i++) s.eeq[i] = c.eeq[i];
-    if (it < 49) { if (!fast_osc(c, s.tq, s.target, s.qvel, s.u)) { *why = BAIL_OSC; return FAST_BAIL; } }
+    if (it < 49) { if (!fast_osc(c, s.tq, s.target, s.qvel, s.u, COOP)) { *why = BAIL_OSC; if (!COOP) return FAST_BAIL; dead |= BAIL_OSC; } }
   }
+  if (dead) { *why = dead; return FAST_BAIL; }
   bool bad = false;
 #pragma unroll
   for (int k = 0; k < JACO_NQ; k++) bad = bad || !(fabsf(s.qpos[k]) < 1e6f);
@@ -946,14 +1096,19 @@ JHD void fast_store(float* state, int N, int i, const FastSim& s) {
 // Fast-path entry for env i.  Returns FAST_BAIL (state untouched, nothing written) or FAST_OK with the state
 // advanced and every output row written; *needs_reset = 1 when the episode ended and auto_reset is on (the
 // caller re-initialises the env with the general reset and overwrites obs_row with the new episode's first obs).
+// COOP = true: the warp-cooperative general path serves this env's contacts (all 32 lanes call together; lanes
+// with active = false shadow env i without writing anything).
+template <bool COOP>
 JHD int entry_step_fast(const JacoCfg& cfg, float* state, int N, int i, int env_id, const float* action_row, float* obs_row,
                         float* reward, unsigned char* done, unsigned char* succ, float* wb, float* term_obs_row, int auto_reset,
-                        float* local_stats, int* needs_reset, int* why) {
+                        float* local_stats, int* needs_reset, int* why, CoopWS* ws = nullptr, bool active = true) {
   FastSim s;
   fast_load(state, N, i, s);
   float obs[JACO_NOBS], r, w; int d, sc;
   *needs_reset = 0;
-  if (fast_env_step(cfg, s, env_id, action_row, obs, &r, &d, &sc, &w, why) != FAST_OK) return FAST_BAIL;
+  int rc = fast_env_step<COOP>(cfg, s, env_id, action_row, obs, &r, &d, &sc, &w, why, ws, active);
+  if (!active) return FAST_OK;
+  if (rc != FAST_OK) return FAST_BAIL;
   s.accum_rew += r;
   local_stats[STAT_STEPS] += 1;
   if (d) {

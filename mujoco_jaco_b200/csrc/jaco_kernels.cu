@@ -8,7 +8,7 @@
 #include <stdlib.h>
 #include <new>
 #include "../../include/jaco_b200.h"
-#include "jaco_fast.cuh"
+#include "jaco_launch.h"
 
 #define JACO_BLOCK 128
 
@@ -24,17 +24,6 @@ struct jaco_sim_handle {
   long long launches;
   char err[256];
 };
-
-__device__ __forceinline__ void block_stats_flush(float* local, float* gstats) {
-  // warp-shuffle reduction of the per-thread counters, one atomic per warp per non-zero counter
-#pragma unroll
-  for (int k = 0; k < 9; k++) {
-    float v = local[k];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if ((threadIdx.x & 31) == 0 && v != 0.0f) atomicAdd(gstats + k, v);
-  }
-}
 
 __global__ void __launch_bounds__(JACO_BLOCK) jaco_reset_kernel(JacoCfg cfg, float* state, int N, int env_offset, const unsigned char* mask, float* obs) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -61,40 +50,7 @@ __global__ void __launch_bounds__(JACO_BLOCK) jaco_step_kernel(JacoCfg cfg, floa
   block_stats_flush(local, gstats);
 }
 
-// ---- two-kernel env step: fast path for every env, general path for the envs that left the fast regime ----
-#ifndef JACO_FAST_BLOCK
-#define JACO_FAST_BLOCK 128
-#endif
-#ifndef JACO_FAST_MINBLOCKS
-#define JACO_FAST_MINBLOCKS 1
-#endif
 #define JACO_LIST_BLOCK 32
-
-__global__ void __launch_bounds__(JACO_FAST_BLOCK, JACO_FAST_MINBLOCKS) jaco_step_fast_kernel(JacoCfg cfg, float* state, int N, int env_offset, const float* action, float* obs, float* reward,
-                                                                    unsigned char* done, unsigned char* succ, float* wb, float* term_obs, int auto_reset, float* gstats,
-                                                                    int* worklist, int* counters) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  float local[16];
-#pragma unroll
-  for (int k = 0; k < 16; k++) local[k] = 0;
-  if (i < N) {
-    float a[JACO_NACT];
-#pragma unroll
-    for (int k = 0; k < JACO_NACT; k++) a[k] = action[(size_t)i * JACO_NACT + k];
-    float r, w; unsigned char d, sc; int needs_reset, why;
-    int rc = entry_step_fast(cfg, state, N, i, env_offset + i, a, obs + (size_t)i * JACO_NOBS, &r, &d, &sc, &w,
-                             term_obs ? term_obs + (size_t)i * JACO_NOBS : nullptr, auto_reset, local, &needs_reset, &why);
-    if (rc == FAST_OK) {
-      reward[i] = r; done[i] = d; succ[i] = sc; wb[i] = w;
-      if (needs_reset) worklist[N + atomicAdd(counters + 1, 1)] = i;
-    } else {
-      worklist[atomicAdd(counters + 0, 1)] = i;
-      int bit = 31 - __clz(why & -why);  // lowest reason bit
-      atomicAdd(counters + 2 + (bit < 0 ? 0 : bit), 1);
-    }
-  }
-  block_stats_flush(local, gstats);
-}
 
 // general path over the bail list, then the general reset over the finished-episode list
 __global__ void __launch_bounds__(JACO_LIST_BLOCK) jaco_step_list_kernel(JacoCfg cfg, float* state, int N, int env_offset, const float* action, float* obs, float* reward,
@@ -177,13 +133,18 @@ int jaco_create(const void* model_blob, size_t nbytes, int n_envs, int task_id, 
   JacoModel* m = new JacoModel();
   jaco_model_from_blob((const double*)model_blob, m);
   cudaError_t e = cudaMemcpyToSymbol(c_jaco_model, m, sizeof(JacoModel));
+  if (e == cudaSuccess) e = cudaMemcpyToSymbol(g_jaco_model_dev, m, sizeof(JacoModel));
   const bool fast_ok = fast_model_ok(*m);
+  if (e == cudaSuccess) e = jaco_fast_upload_model(m);
+  if (e == cudaSuccess) e = jaco_coop_upload_model(m);
   delete m;
   CK(e);
   CK(cudaMalloc(&h->state, sizeof(float) * JACO_NSTATE * (size_t)n_envs));
   CK(cudaMemset(h->state, 0, sizeof(float) * JACO_NSTATE * (size_t)n_envs));
   h->use_fast = fast_ok ? 1 : 0;
-  if (getenv("JACO_NO_FAST")) h->use_fast = 0;
+  if (h->use_fast) h->use_fast = 2;                      /* default: hybrid fast + warp-cooperative kernel */
+  if (getenv("JACO_NO_COOP") && h->use_fast) h->use_fast = 1;  /* diagnostics: fast kernel with bail-out to the general list kernel */
+  if (getenv("JACO_NO_FAST")) h->use_fast = 0;           /* diagnostics: general thread-per-env kernel only */
   CK(cudaMalloc(&h->worklist, sizeof(int) * 2 * (size_t)n_envs));
   CK(cudaMalloc(&h->counters, sizeof(int) * 16));
   CK(cudaMemset(h->counters, 0, sizeof(int) * 16));
@@ -207,6 +168,7 @@ int jaco_debug_counters(jaco_handle h, int* out16) {  /* host copy of the work-l
   CK(cudaMemcpy(out16, h->counters, 16 * sizeof(int), cudaMemcpyDeviceToHost));
   return JACO_OK;
 }
+int jaco_debug_prof(unsigned long long* out16) { return jaco_coop_prof(out16); }
 int jaco_n_envs(jaco_handle h) { return h ? h->n : 0; }
 long long jaco_launch_count(jaco_handle h) { return h ? h->launches : 0; }
 
@@ -225,8 +187,8 @@ int jaco_step(jaco_handle h, const float* action, float* obs, float* reward, uin
   cudaStream_t st = (cudaStream_t)stream;
   if (h->use_fast) {
     CK(cudaMemsetAsync(h->counters, 0, 2 * sizeof(int), st));
-    jaco_step_fast_kernel<<<(h->n + JACO_FAST_BLOCK - 1) / JACO_FAST_BLOCK, JACO_FAST_BLOCK, 0, st>>>(h->cfg, h->state, h->n, h->env_offset, action, obs, reward, done, succ, wb,
-                                                                                                   term_obs, auto_reset, h->stats, h->worklist, h->counters);
+    JacoStepArgs A = {h->cfg, h->state, h->n, h->env_offset, action, obs, reward, done, succ, wb, term_obs, auto_reset, h->stats, h->worklist, h->counters};
+    CK(h->use_fast == 2 ? jaco_coop_launch(A, st) : jaco_fast_launch(A, st));
     if (!getenv("JACO_FAST_ONLY"))  /* timing experiments only: skips the general pass, results are then incomplete */
     jaco_step_list_kernel<<<(h->n + JACO_LIST_BLOCK - 1) / JACO_LIST_BLOCK, JACO_LIST_BLOCK, 0, st>>>(h->cfg, h->state, h->n, h->env_offset, action, obs, reward, done, succ, wb,
                                                                                                    term_obs, auto_reset, h->stats, h->worklist, h->counters);

@@ -1,0 +1,35 @@
+// jaco_launch.h -- internal glue between the translation units of libjaco_b200.so (each .cu is compiled on its
+// own so the three big kernels build in parallel; every unit keeps its own copy of the model symbols).
+#pragma once
+#include <cuda_runtime.h>
+#include "../../include/jaco_b200.h"
+#include "jaco_fast.cuh"
+
+#ifndef JACO_FAST_BLOCK
+#define JACO_FAST_BLOCK 128
+#endif
+#ifndef JACO_FAST_MINBLOCKS
+#define JACO_FAST_MINBLOCKS 1
+#endif
+
+__device__ __forceinline__ void block_stats_flush(float* local, float* gstats) {
+  // warp-shuffle reduction of the per-thread counters, one atomic per warp per non-zero counter
+#pragma unroll
+  for (int k = 0; k < 9; k++) {
+    float v = local[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0 && v != 0.0f) atomicAdd(gstats + k, v);
+  }
+}
+
+struct JacoStepArgs {
+  JacoCfg cfg; float* state; int N, env_offset; const float* action; float* obs; float* reward;
+  unsigned char* done; unsigned char* succ; float* wb; float* term_obs; int auto_reset; float* gstats; int* worklist; int* counters;
+};
+// jaco_kernel_fast.cu / jaco_kernel_coop.cu
+cudaError_t jaco_fast_upload_model(const JacoModel* m);
+cudaError_t jaco_fast_launch(const JacoStepArgs& a, cudaStream_t st);
+cudaError_t jaco_coop_upload_model(const JacoModel* m);
+cudaError_t jaco_coop_launch(const JacoStepArgs& a, cudaStream_t st);
+int jaco_coop_prof(unsigned long long* out16);

@@ -14,15 +14,18 @@
 
 #ifdef __CUDACC__
 #define JHD __host__ __device__ inline
-__constant__ JacoModel c_jaco_model;
+static __constant__ JacoModel c_jaco_model;   // uniform (same address in every lane) accesses: the per-thread paths
+static __device__ JacoModel g_jaco_model_dev; // lane-varying accesses (pairs / geoms indexed by lane): the cooperative path
 #else
 #define JHD inline
 #endif
 static JacoModel g_jaco_model_host;
 #ifdef __CUDA_ARCH__
 #define MDL c_jaco_model
+#define MDLG g_jaco_model_dev
 #else
 #define MDL g_jaco_model_host
+#define MDLG g_jaco_model_host
 #endif
 
 #define JPI 3.14159265358979323846f
@@ -187,6 +190,8 @@ JHD void philox4x32(uint64_t seed, uint32_t c0, uint32_t c1, uint32_t c2, uint32
 struct JacoCfg { int task, variant, obs_mode, task_max_steps; uint64_t seed; };
 
 struct JacoSim {
+  static const int MAXC = JACO_MAXCON;
+  static JHD const JacoModel& model() { return MDL; }
   // state
   float qpos[JACO_NQ], qvel[JACO_NV], warm[JACO_NV], ctrl[JACO_NU];
   // kinematics (index = body id: 0 world, 1..9 chain, 10 object, 11 dest)
@@ -449,18 +454,27 @@ JHD void forward_chain_smooth(JacoSim& s) {
 }
 
 // ------------------------------------------------------------------------------------------- collision
+// squared distance from point c to an oriented box (centre bp, rows of bR = world-from-box, half sizes h)
+JHD float point_box_dist2(const float* c, const float* bp, const float* bR, const float* h) {
+  float d[3], l[3];
+  v3sub(d, c, bp); m3tmulv(l, bR, d);
+  float e0 = fmaxf(fabsf(l[0]) - h[0], 0.0f), e1 = fmaxf(fabsf(l[1]) - h[1], 0.0f), e2 = fmaxf(fabsf(l[2]) - h[2], 0.0f);
+  return e0 * e0 + e1 * e1 + e2 * e2;
+}
 JHD void make_frame(const float* n, float* t1, float* t2) {  // mju_makeFrame
   if (fabsf(n[1]) < 0.5f) v3set(t1, 0, 1, 0); else v3set(t1, 0, 0, 1);
   float d = v3dot(n, t1); v3addscl(t1, t1, n, -d);
   float inv = 1.0f / v3norm(t1); t1[0] *= inv; t1[1] *= inv; t1[2] *= inv;
   v3cross(t2, n, t1);
 }
-JHD void add_contact(JacoSim& s, int pair, const float* pos, const float* n, float dist) {
-  if (s.ncon >= JACO_MAXCON) return;
+template <class K>
+JHD void add_contact(K& s, int pair, const float* pos, const float* n, float dist) {
+  if (s.ncon >= K::MAXC) return;
   int c = s.ncon++;
   v3copy(s.cpos[c], pos); v3copy(s.cn[c], n); s.cdist[c] = dist; s.cpair[c] = pair;
 }
-JHD void collide_plane_box(JacoSim& s, int pair, const float* pp, const float* pR, const float* bp, const float* bR, const float* size, float margin) {
+template <class K>
+JHD void collide_plane_box(K& s, int pair, const float* pp, const float* pR, const float* bp, const float* bR, const float* size, float margin) {
   float n[3] = {pR[2], pR[5], pR[8]}, d[3];
   v3sub(d, bp, pp);
   float dist = v3dot(d, n);
@@ -510,7 +524,8 @@ JHD float seg_box_dfdt(const float* p0, const float* d, const float* h, float t)
   for (int i = 0; i < 3; i++) { float x = p0[i] + t * d[i]; if (x > h[i]) s += (x - h[i]) * d[i]; else if (x < -h[i]) s += (x + h[i]) * d[i]; }
   return s;
 }
-JHD void collide_capsule_box(JacoSim& s, int pair, int box_first, const float* cpn, const float* cR, const float* csize, const float* bp, const float* bR, const float* bsize, float margin) {
+template <class K>
+JHD void collide_capsule_box(K& s, int pair, int box_first, const float* cpn, const float* cR, const float* csize, const float* bp, const float* bR, const float* bsize, float margin) {
   float ax[3] = {cR[2], cR[5], cR[8]}, p0[3], p1[3], r = csize[0];
   v3addscl(p0, cpn, ax, -csize[1]); v3addscl(p1, cpn, ax, csize[1]);
   float nrm[3], dist, pos[3], sgn = box_first ? 1.0f : -1.0f;
@@ -538,7 +553,8 @@ JHD void collide_capsule_box(JacoSim& s, int pair, int box_first, const float* c
   float c[3]; v3addscl(c, p0, d, ts);
   if (sphere_box(c, r, bp, bR, bsize, margin, nrm, &dist, pos)) { float n2[3] = {sgn * nrm[0], sgn * nrm[1], sgn * nrm[2]}; add_contact(s, pair, pos, n2, dist); }
 }
-JHD void collide_plane_capsule(JacoSim& s, int pair, const float* pp, const float* pR, const float* cpn, const float* cR, const float* csize, float margin) {
+template <class K>
+JHD void collide_plane_capsule(K& s, int pair, const float* pp, const float* pR, const float* cpn, const float* cR, const float* csize, float margin) {
   float n[3] = {pR[2], pR[5], pR[8]}, ax[3] = {cR[2], cR[5], cR[8]};
 #pragma unroll
   for (int sg = -1; sg <= 1; sg += 2) {
@@ -551,7 +567,8 @@ JHD void collide_plane_capsule(JacoSim& s, int pair, const float* pp, const floa
   }
 }
 // box-box: SAT over 15 axes, then face clipping (<= 8 points) or one edge-edge point (DESIGN.md "collision")
-JHD void collide_box_box(JacoSim& s, int pair, const float* pa, const float* Ra, const float* ha, const float* pb, const float* Rb, const float* hb, float margin) {
+template <class K>
+JHD void collide_box_box(K& s, int pair, const float* pa, const float* Ra, const float* ha, const float* pb, const float* Rb, const float* hb, float margin) {
   float t[3], A[3][3], B[3][3], C[3][3], AC[3][3];
   v3sub(t, pb, pa);
 #pragma unroll
@@ -662,34 +679,39 @@ static long long g_cstats[16];
 #else
 #define CSTAT(i)
 #endif
+// one geom pair: group culling by the hand sphere hs, bounding-sphere cull, narrow phase into sink k.
+// PS supplies the body poses (bx, bR); K receives the contacts (add_contact).
+template <class PS, class K>
+JHD void collide_pair(const PS& s, int p, const float* hs, K& k) {
+  const JacoModel& m = PS::model();
+  const JacoPair& P = m.pairs[p];
+  const JacoGeom& G1 = m.geoms[P.g1]; const JacoGeom& G2 = m.geoms[P.g2];
+  float p1[3], p2[3];
+  { float u[3]; m3mulv(u, s.bR[G1.body], G1.pos); v3add(p1, s.bx[G1.body], u); m3mulv(u, s.bR[G2.body], G2.pos); v3add(p2, s.bx[G2.body], u); }
+  if (P.group >= 1 && P.group <= 4) {
+    const JacoGeom& O = (P.group == 1) ? G2 : G1; const float* po = (P.group == 1) ? p2 : p1;
+    float d[3]; v3sub(d, hs, po);
+    if (O.type != JACO_GEOM_PLANE) { if (v3norm(d) > m.hand_sphere[3] + O.rbound + P.margin) return; }
+    else { if (d[2] > m.hand_sphere[3] + P.margin) return; }
+    CSTAT(P.group);
+  }
+  if (G1.type != JACO_GEOM_PLANE && G2.type != JACO_GEOM_PLANE) { float d[3]; v3sub(d, p1, p2); if (v3norm(d) > G1.rbound + G2.rbound + P.margin) return; }
+  CSTAT(5 + P.group);
+  float R1[9], R2[9];
+  m3mul(R1, s.bR[G1.body], G1.R); m3mul(R2, s.bR[G2.body], G2.R);
+  if (G1.type == JACO_GEOM_PLANE && G2.type == JACO_GEOM_BOX) collide_plane_box(k, p, p1, R1, p2, R2, G2.size, P.margin);
+  else if (G1.type == JACO_GEOM_PLANE && G2.type == JACO_GEOM_CAPSULE) collide_plane_capsule(k, p, p1, R1, p2, R2, G2.size, P.margin);
+  else if (G1.type == JACO_GEOM_BOX && G2.type == JACO_GEOM_BOX) collide_box_box(k, p, p1, R1, G1.size, p2, R2, G2.size, P.margin);
+  else if (G1.type == JACO_GEOM_BOX && G2.type == JACO_GEOM_CAPSULE) collide_capsule_box(k, p, 1, p2, R2, G2.size, p1, R1, G1.size, P.margin);
+  else if (G1.type == JACO_GEOM_CAPSULE && G2.type == JACO_GEOM_BOX) collide_capsule_box(k, p, 0, p1, R1, G1.size, p2, R2, G2.size, P.margin);
+}
 JHD void collision(JacoSim& s) {
   const JacoModel& m = MDL;
   s.ncon = 0;
   CSTAT(0);
   float hs[3], t[3];
   m3mulv(t, s.bR[6], m.hand_sphere); v3add(hs, s.bx[6], t);
-  for (int p = 0; p < JM_NPAIR; p++) {
-    const JacoPair& P = m.pairs[p];
-    const JacoGeom& G1 = m.geoms[P.g1]; const JacoGeom& G2 = m.geoms[P.g2];
-    float p1[3], p2[3];
-    { float u[3]; m3mulv(u, s.bR[G1.body], G1.pos); v3add(p1, s.bx[G1.body], u); m3mulv(u, s.bR[G2.body], G2.pos); v3add(p2, s.bx[G2.body], u); }
-    if (P.group >= 1 && P.group <= 4) {
-      const JacoGeom& O = (P.group == 1) ? G2 : G1; const float* po = (P.group == 1) ? p2 : p1;
-      float d[3]; v3sub(d, hs, po);
-      if (O.type != JACO_GEOM_PLANE) { if (v3norm(d) > m.hand_sphere[3] + O.rbound + P.margin) continue; }
-      else { if (d[2] > m.hand_sphere[3] + P.margin) continue; }
-      CSTAT(P.group);
-    }
-    if (G1.type != JACO_GEOM_PLANE && G2.type != JACO_GEOM_PLANE) { float d[3]; v3sub(d, p1, p2); if (v3norm(d) > G1.rbound + G2.rbound + P.margin) continue; }
-    CSTAT(5 + P.group);
-    float R1[9], R2[9];
-    m3mul(R1, s.bR[G1.body], G1.R); m3mul(R2, s.bR[G2.body], G2.R);
-    if (G1.type == JACO_GEOM_PLANE && G2.type == JACO_GEOM_BOX) collide_plane_box(s, p, p1, R1, p2, R2, G2.size, P.margin);
-    else if (G1.type == JACO_GEOM_PLANE && G2.type == JACO_GEOM_CAPSULE) collide_plane_capsule(s, p, p1, R1, p2, R2, G2.size, P.margin);
-    else if (G1.type == JACO_GEOM_BOX && G2.type == JACO_GEOM_BOX) collide_box_box(s, p, p1, R1, G1.size, p2, R2, G2.size, P.margin);
-    else if (G1.type == JACO_GEOM_BOX && G2.type == JACO_GEOM_CAPSULE) collide_capsule_box(s, p, 1, p2, R2, G2.size, p1, R1, G1.size, P.margin);
-    else if (G1.type == JACO_GEOM_CAPSULE && G2.type == JACO_GEOM_BOX) collide_capsule_box(s, p, 0, p1, R1, G1.size, p2, R2, G2.size, P.margin);
-  }
+  for (int p = 0; p < JM_NPAIR; p++) collide_pair(s, p, hs, s);
 }
 
 // ------------------------------------------------------------------------------------------- constraints
@@ -713,20 +735,23 @@ JHD void row_params(const float* solref, const float* solimp, float pos, float m
   *imp = impedance(solimp, pos - margin);
   *R = fmaxf(JMINVAL, (1 - *imp) * diagApprox / *imp);
 }
-JHD int contact_dim(int c, const JacoSim& s) { return MDL.pairs[s.cpair[c]].condim; }
+template <class S>
+JHD int contact_dim(int c, const S& s) { return S::model().pairs[s.cpair[c]].condim; }
 JHD float contact_mu(const JacoPair& P, int k) { return k <= 2 ? P.friction[0] : (k == 3 ? P.friction[1] : P.friction[2]); }  // k = 1..5
 
 // relative point motion at a contact for body twists (W, V): u = linear (b2 - b1) at pos, w = angular (b2 - b1)
-JHD void contact_rel(const JacoSim& s, int c, float W[JACO_NBODY][3], float V[JACO_NBODY][3], float* u, float* w) {
-  const JacoPair& P = MDL.pairs[s.cpair[c]];
-  int b1 = MDL.geoms[P.g1].body, b2 = MDL.geoms[P.g2].body;
+template <class S>
+JHD void contact_rel(const S& s, int c, const float W[JACO_NBODY][3], const float V[JACO_NBODY][3], float* u, float* w) {
+  const JacoPair& P = S::model().pairs[s.cpair[c]];
+  int b1 = S::model().geoms[P.g1].body, b2 = S::model().geoms[P.g2].body;
   float r[3], t[3], u1[3], u2[3];
   v3sub(r, s.cpos[c], s.bx[b1]); v3cross(t, W[b1], r); v3add(u1, V[b1], t);
   v3sub(r, s.cpos[c], s.bx[b2]); v3cross(t, W[b2], r); v3add(u2, V[b2], t);
   v3sub(u, u2, u1); v3sub(w, W[b2], W[b1]);
 }
 // six frame components (n,t1,t2 of u ; n,t1,t2 of w)
-JHD void contact_comp(const JacoSim& s, int c, const float* u, const float* w, float* out) {
+template <class S>
+JHD void contact_comp(const S& s, int c, const float* u, const float* w, float* out) {
   float t1[3], t2[3];
   make_frame(s.cn[c], t1, t2);
   out[0] = v3dot(s.cn[c], u); out[1] = v3dot(t1, u); out[2] = v3dot(t2, u);
@@ -868,13 +893,14 @@ JHD void rows_force(JacoSim& s, float* out) {
   for (int r = 0; r < s.nlim; r++) if (s.le[r] < 0) out[s.ldof[r]] += s.lsign[r] * (-s.lD[r] * s.le[r]);
 }
 // dense Jacobian row pieces of one contact direction (dl linear, dr angular) -> j[21]
-JHD void contact_row(const JacoSim& s, int c, const float* dl, const float* dr, float* j) {
-  const JacoPair& P = MDL.pairs[s.cpair[c]];
+template <class S>
+JHD void contact_row(const S& s, int c, const float* dl, const float* dr, float* j) {
+  const JacoPair& P = S::model().pairs[s.cpair[c]];
 #pragma unroll
   for (int i = 0; i < JACO_NV; i++) j[i] = 0;
 #pragma unroll
   for (int side = 0; side < 2; side++) {
-    int b = side ? MDL.geoms[P.g2].body : MDL.geoms[P.g1].body; float sg = side ? 1.0f : -1.0f;
+    int b = side ? S::model().geoms[P.g2].body : S::model().geoms[P.g1].body; float sg = side ? 1.0f : -1.0f;
     if (b == 0) continue;
     if (b <= 9) {
       int k = b - 1;

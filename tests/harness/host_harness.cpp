@@ -71,7 +71,9 @@ extern "C" void hh_step_fast(int task, int variant, unsigned long long seed, int
   JacoCfg c = mkcfg(task, variant, seed);
   for (int i = 0; i < N; i++) {
     int nr = 0; why[i] = 0;
-    int rc = entry_step_fast(c, state, N, i, env_offset + i, action + (size_t)i * 7, obs + (size_t)i * JACO_NOBS, reward + i, done + i, succ + i, wb + i, 0, auto_reset, stats16, &nr, why + i);
+    static CoopWS ws;
+    int rc = allow_fallback == 2 ? entry_step_fast<true>(c, state, N, i, env_offset + i, action + (size_t)i * 7, obs + (size_t)i * JACO_NOBS, reward + i, done + i, succ + i, wb + i, 0, auto_reset, stats16, &nr, why + i, &ws, true)
+           : entry_step_fast<false>(c, state, N, i, env_offset + i, action + (size_t)i * 7, obs + (size_t)i * JACO_NOBS, reward + i, done + i, succ + i, wb + i, 0, auto_reset, stats16, &nr, why + i);
     if (rc == FAST_OK) { if (nr) entry_reset(c, state, N, i, env_offset + i, obs + (size_t)i * JACO_NOBS); }
     else if (allow_fallback) entry_step(c, state, N, i, env_offset + i, action + (size_t)i * 7, obs + (size_t)i * JACO_NOBS, reward + i, done + i, succ + i, wb + i, 0, auto_reset, stats16);
   }
@@ -86,3 +88,5 @@ extern "C" void hh_fast_chain(const float* q9, const float* v9, const float* O, 
   memcpy(bias9, c.bias, 36); memcpy(J36, c.J, 144); memcpy(eepos, c.eepos, 12); memcpy(eeq, c.eeq, 16);
 }
 extern "C" void hh_body_spheres(float* out16) { memcpy(out16, g_jaco_model_host.body_sphere, 64); }
+extern "C" void hh_scale_spheres(float f) { for (int b = 0; b < 4; b++) g_jaco_model_host.body_sphere[b][3] *= f; }
+extern "C" int hh_sizeof_coopws() { return (int)sizeof(CoopWS); }
