@@ -40,6 +40,9 @@ static __device__ unsigned long long g_jprof[16];
 #define COOP_FORCE_B 2      // active joint limit or non-simple scene contacts: stage B regardless of the arm proximity
 #define COOP_NROW 128   // pool of direction-Jacobian rows (3 per condim-3 contact, 6 per condim-6 contact)
 
+#if defined(JACO_COLLISION_STATS) && !defined(__CUDACC__)
+static long long g_coop_pairA[64], g_coop_pairC[64];   // CPU harness only: per-pair stage-A survivors / pairs with contacts
+#endif
 struct CoopSink {  // contacts of one geom pair (<= 8: box-box clipping cap)
   static const int MAXC = 8;
   int ncon, cpair[8];
@@ -109,6 +112,9 @@ JHD int coop_stageA(CoopWS& w) {
   unsigned c0 = 0, c1 = 0;
   for (int l = 0; l < 32; l++) { if (w.red[l][0] != 0.0f) c0 |= 1u << l; if (w.red[l][1] != 0.0f) c1 |= 1u << l; }
   COOP_SYNC();
+#if defined(JACO_COLLISION_STATS) && !defined(__CUDACC__)
+  for (int l = 0; l < 32; l++) { if ((c0 >> l) & 1) g_coop_pairA[l]++; if ((c1 >> l) & 1) g_coop_pairA[32 + l]++; }
+#endif
   COOP_LANE0 { w.cand[0] = c0 | 0xFu; w.cand[1] = c1; }   // scene pairs 0..3 always go through the narrow phase
   COOP_SYNC();
   return (c0 | c1) != 0 || (w.flags & COOP_FORCE_B) != 0;
@@ -126,6 +132,9 @@ JHD void coop_collision(CoopWS& w) {
       CoopSink& k = w.sink[lane];
       k.ncon = 0;
       if (p < JM_NPAIR && ((w.cand[round] >> lane) & 1u)) collide_pair(w, p, hs, k);
+#if defined(JACO_COLLISION_STATS) && !defined(__CUDACC__)
+      if (k.ncon > 0) g_coop_pairC[p]++;
+#endif
     } COOP_END
     COOP_BEGIN {
       int off = base;

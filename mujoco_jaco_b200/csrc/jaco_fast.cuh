@@ -21,6 +21,15 @@
 // bail reasons (bit mask, statistics only)
 enum { BAIL_LIMIT = 1, BAIL_HAND = 2, BAIL_FOREARM = 4, BAIL_OBJ = 8, BAIL_DEST = 16, BAIL_OSC = 32, BAIL_NAN = 64 };
 
+#if defined(JACO_COLLISION_STATS) && !defined(__CUDACC__)
+static long long g_fast_wstats[16];   // CPU harness only: workload mix of the hybrid step (scripts/workload_mix.py)
+#define FAST_WSTAT(k) g_fast_wstats[k]++
+#define FAST_WSTAT_ADD(k, v) g_fast_wstats[k] += (v)
+#else
+#define FAST_WSTAT(k)
+#define FAST_WSTAT_ADD(k, v)
+#endif
+
 struct FastSim {
   float qpos[JACO_NQ], qvel[JACO_NV], warm[JACO_NV];
   float u[6];                 // OSC torque for the coming substep (built from the previous forward: SURVEY 3.1 lag)
@@ -999,11 +1008,18 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
         __syncwarp();
       }
 #else
+      FAST_WSTAT(0);
       if (need) {
+        FAST_WSTAT(1);
+        if (bail & BAIL_LIMIT) FAST_WSTAT(8);
+        if (bail & (BAIL_HAND | BAIL_FOREARM)) FAST_WSTAT(9);
+        if (bail & (BAIL_OBJ | BAIL_DEST)) FAST_WSTAT(10);
         coop_publish_poses(*ws, c, fo, fd, flags);
         if (coop_stageA(*ws)) {
+          FAST_WSTAT(2);
           coop_publish(*ws, s, c, fo, fd, fsm, it == 49);
           solved = coop_stageB(*ws);
+          if (solved) { FAST_WSTAT(3); FAST_WSTAT_ADD(4, ws->iters); FAST_WSTAT_ADD(5, ws->ncon); if (solved & 1) FAST_WSTAT(6); if (ws->ncon > 0) FAST_WSTAT(7); }
           if (solved) { for (int i = 0; i < JACO_NV; i++) { qacc_g[i] = ws->qacc[i]; fcon_g[i] = ws->fcon[i]; } if (it == 49) s.touch_now = touch_class(ws->touch); }
         }
       }

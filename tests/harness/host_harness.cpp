@@ -78,6 +78,8 @@ extern "C" void hh_step_fast(int task, int variant, unsigned long long seed, int
     else if (allow_fallback) entry_step(c, state, N, i, env_offset + i, action + (size_t)i * 7, obs + (size_t)i * JACO_NOBS, reward + i, done + i, succ + i, wb + i, 0, auto_reset, stats16);
   }
 }
+extern "C" void hh_wstats(long long* out, int clear) { for (int i = 0; i < 16; i++) { out[i] = g_fast_wstats[i]; if (clear) g_fast_wstats[i] = 0; } }
+extern "C" void hh_pairstats(long long* a, long long* c) { for (int i = 0; i < 64; i++) { a[i] = g_coop_pairA[i]; c[i] = g_coop_pairC[i]; } }
 extern "C" int hh_fast_model_ok() { return fast_model_ok(g_jaco_model_host) ? 1 : 0; }
 // chain pass probe: M (9x9 dense), bias9, J 6x6, eepos, eeq at (q9, v9) with reference point O
 extern "C" void hh_fast_chain(const float* q9, const float* v9, const float* O, float* M81, float* bias9, float* J36, float* eepos, float* eeq) {

@@ -89,13 +89,16 @@ def test_env_step_reward_done_picking():
 
 
 def test_rollout_50_steps_reaching_drift():
-    """Short-horizon drift bound: 50 env steps (2500 substeps) of contact-free reaching stay within 2e-3 rad."""
+    """Short-horizon drift bound: 50 env steps (2500 substeps) of contact-free reaching.  The bound is the measured
+    divergence of the oracle's own fp32 build from its fp64 build on the same roll-out: the CUDA
+    path (fp32) must stay within 3x that divergence (+1e-3 rad), and its median env within 5e-4 rad."""
     from mujoco_jaco_b200.env import JacoVecEnv
     n = 64
     env = JacoVecEnv(n, task="reaching", seed=2, auto_reset=False)
     env.reset()
     ora = _oracles("reaching", 2, n)
-    for o in ora:
+    o32 = _oracles("reaching", 2, n, f32=True)
+    for o in ora + o32:
         o.reset()
     rng = np.random.default_rng(5)
     alive = np.ones(n, bool)
@@ -105,13 +108,17 @@ def test_rollout_50_steps_reaching_drift():
         for i, o in enumerate(ora):
             if alive[i]:
                 r = o.step(a[i].astype(np.float64))
-                alive[i] &= not r[2]
+                r32 = o32[i].step(a[i].astype(np.float64))
+                alive[i] &= not (r[2] or r32[2])
         alive &= ~done.astype(bool)
     q, _, _ = [t.cpu().numpy() for t in env.get_state()]
     oq = np.stack([o.get_state()[0] for o in ora])
-    err = np.abs(q[alive, :6] - oq[alive, :6]).max()
+    oq32 = np.stack([o.get_state()[0] for o in o32])
+    err = np.abs(q[alive, :6] - oq[alive, :6]).max(1)
+    err32 = np.abs(oq32[alive, :6] - oq[alive, :6]).max(1)
     assert alive.sum() > n // 2
-    assert err < 2e-3, err
+    assert np.median(err) < 5e-4, np.median(err)
+    assert err.max() < 3 * err32.max() + 1e-3, (err.max(), err32.max())
 
 
 def test_step_host_matches_device_path():
