@@ -56,6 +56,9 @@ struct CoopWS {
   float qpos9[9], qvel[JACO_NV], Mc[45], Mf[2][21], asm_[JACO_NV], warm[JACO_NV];
   int want_touch, flags;      // flags: COOP_SIMPLE_OBJ | COOP_FORCE_B
   unsigned cand[2];           // stage A: candidate bit per geom pair (pairs >= 4; scene pairs are always tested in stage B)
+  // ---- arm contacts the owner thread found with its own narrow phase (fast_arm_collide), in pair order
+  int pre_ncon, pre_pair[24];
+  float pre_pos[24][3], pre_n[24][3], pre_dist[24];
   // ---- contacts and rows
   int ncon, nlim, arm_rows;
   int cpair[JACO_MAXCON], cmask[JACO_MAXCON], ccond[JACO_MAXCON], croff[JACO_MAXCON];
@@ -127,6 +130,7 @@ JHD void coop_collision(CoopWS& w) {
   { float t[3]; m3mulv(t, w.bR[6], m.hand_sphere); v3add(hs, w.bx[6], t); }
   int base = 0;
   for (int round = 0; round < (JM_NPAIR + 31) / 32; round++) {
+    if (w.cand[round] == 0u) continue;   // uniform: nothing to test in this round
     COOP_BEGIN {
       int p = round * 32 + lane;
       CoopSink& k = w.sink[lane];
@@ -150,6 +154,14 @@ JHD void coop_collision(CoopWS& w) {
     for (int l = 0; l < 32; l++) tot += w.sink[l].ncon;
     base = base + tot > JACO_MAXCON ? JACO_MAXCON : base + tot;
   }
+  COOP_BEGIN {  // append the owner's pre-collided arm contacts (pair indices >= 4, already in pair order)
+    const int j = lane;
+    if (j < w.pre_ncon && base + j < JACO_MAXCON) {
+      const int c = base + j;
+      v3copy(w.cpos[c], w.pre_pos[j]); v3copy(w.cn[c], w.pre_n[j]); w.cdist[c] = w.pre_dist[j]; w.cpair[c] = w.pre_pair[j];
+    }
+  } COOP_END
+  base = base + w.pre_ncon > JACO_MAXCON ? JACO_MAXCON : base + w.pre_ncon;
   COOP_SYNC();
   COOP_LANE0 { w.ncon = base; }
   COOP_SYNC();

@@ -854,6 +854,93 @@ JHD void coop_publish(CoopWS& w, const FastSim& s, const ChainOut& c, const Free
   w.want_touch = want_touch;
 }
 
+// ------------------------------------------------------------------------------------------- thread-local arm collision
+// The owner thread's own broad + narrow phase over the arm pairs (model pairs 4..59: an arm geom against the
+// holder / floor / object / dest).  Every lane that is near the scene runs it for its own environment at the same
+// time, so the warp pays for the slowest lane instead of the sum over lanes; the warp-cooperative stage B is then
+// entered only by lanes that actually found contacts (or have an active joint limit / non-simple scene contacts).
+// Semantics: collide_pair of jaco_sim.cuh in pair order, i.e. exactly what coop_collision would have produced for
+// the candidate pairs; the sink holds at most MAXC arm contacts (the scene contacts of pairs 0..3 come first in
+// the workspace, the total is capped at JACO_MAXCON there).
+struct LocalSink {
+  static const int MAXC = 24;
+  int ncon, cpair[MAXC];
+  float cpos[MAXC][3], cn[MAXC][3], cdist[MAXC];
+};
+struct LocalPoses {
+  static JHD const JacoModel& model() { return MDLG; }
+  const float* bx[JACO_NBODY];
+  const float* bR[JACO_NBODY];
+};
+#ifdef __CUDACC__
+#define JNOINLINE __noinline__
+#else
+#define JNOINLINE __attribute__((noinline))
+#endif
+JHD JNOINLINE void fast_arm_collide(const ChainOut& c, const FreeBody& fo, const FreeBody& fd, LocalSink& k) {
+  const JacoModel& m = MDL;
+  const float Z3[3] = {0, 0, 0}, I9[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+  LocalPoses ps;
+  ps.bx[0] = Z3; ps.bR[0] = I9;
+  ps.bx[1] = ps.bx[2] = Z3; ps.bR[1] = ps.bR[2] = I9;   // bodies 1, 2 carry no collision geoms
+#pragma unroll
+  for (int b = 3; b <= 9; b++) { ps.bx[b] = c.bp[b - 3]; ps.bR[b] = c.bRm[b - 3]; }
+  ps.bx[10] = fo.x; ps.bR[10] = fo.R; ps.bx[11] = fd.x; ps.bR[11] = fd.R;
+  k.ncon = 0;
+  // ---- stage A: bounding sphere of the arm geom against the exact scene box / plane (uniform loop: constant-bank reads)
+  unsigned long long cand = 0;
+  for (int p = 4; p < JM_NPAIR; p++) {
+    const JacoPair& P = m.pairs[p];
+    const bool arm1 = m.geoms[P.g1].body >= 1 && m.geoms[P.g1].body <= 9;
+    const JacoGeom& A = arm1 ? m.geoms[P.g1] : m.geoms[P.g2];
+    const JacoGeom& S = arm1 ? m.geoms[P.g2] : m.geoms[P.g1];
+    float cc[3], t[3], sp[3], R[9];
+    m3mulv(t, ps.bR[A.body], A.pos); v3add(cc, ps.bx[A.body], t);
+    const float rr = A.rbound + P.margin + 1e-5f;
+    m3mulv(t, ps.bR[S.body], S.pos); v3add(sp, ps.bx[S.body], t); m3mul(R, ps.bR[S.body], S.R);
+    bool hit;
+    if (S.type == JACO_GEOM_PLANE) { float d[3]; v3sub(d, cc, sp); hit = !(d[0] * R[2] + d[1] * R[5] + d[2] * R[8] > rr); }
+    else if (S.type == JACO_GEOM_BOX) hit = !(point_box_dist2(cc, sp, R, S.size) > rr * rr);
+    else hit = true;
+    if (hit) cand |= 1ull << p;
+  }
+  if (!cand) return;
+  // ---- narrow phase, one routine at a time so that lanes working on different pairs stay converged
+  float hs[3];
+  { float t[3]; m3mulv(t, ps.bR[6], m.hand_sphere); v3add(hs, ps.bx[6], t); }
+  // contacts must come out in pair order: collect per routine, then merge by pair index
+  LocalSink tmp; tmp.ncon = 0;
+  const unsigned long long masks[3] = {m.pm_boxbox, m.pm_capbox, m.pm_plane};
+  for (int r = 0; r < 3; r++) {
+    unsigned long long w = cand & masks[r];
+    while (w) {
+#ifdef __CUDA_ARCH__
+      const int p = __ffsll((long long)w) - 1;
+#else
+      const int p = __builtin_ffsll((long long)w) - 1;
+#endif
+      w &= w - 1;
+      collide_pair(ps, p, hs, tmp);
+    }
+  }
+  // stable merge by pair index (few contacts; contacts of one pair are contiguous and keep their order)
+  for (int p = 4; p < JM_NPAIR && k.ncon < tmp.ncon; p++) {
+    if (!((cand >> p) & 1ull)) continue;
+    for (int j = 0; j < tmp.ncon; j++) if (tmp.cpair[j] == p) {
+      const int d = k.ncon++;
+      v3copy(k.cpos[d], tmp.cpos[j]); v3copy(k.cn[d], tmp.cn[j]); k.cdist[d] = tmp.cdist[j]; k.cpair[d] = p;
+    }
+  }
+}
+
+// Owner thread -> warp workspace: its pre-collided arm contacts; stage B then runs its narrow phase on the scene
+// pairs 0..3 only.
+JHD void coop_publish_contacts(CoopWS& w, const LocalSink& k, int flags) {
+  w.flags = flags; w.cand[0] = 0xFu; w.cand[1] = 0u;
+  w.pre_ncon = k.ncon;
+  for (int j = 0; j < k.ncon; j++) { v3copy(w.pre_pos[j], k.cpos[j]); v3copy(w.pre_n[j], k.cn[j]); w.pre_dist[j] = k.cdist[j]; w.pre_pair[j] = k.cpair[j]; }
+}
+
 JHD int touch_class(const float* touch) {  // env_mujoco_util.py:470-490 on the 20 sensor readings
   const float th = 0.001f;
   int thumb = 0, index = 0, pinky = 0, inner = 0, outer = 0;
@@ -982,19 +1069,19 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
     if (COOP) {
       const bool need = active && !dead && bail != 0;
       const int flags = ((bail & (BAIL_OBJ | BAIL_DEST)) ? 0 : COOP_SIMPLE_OBJ) | ((bail & (BAIL_LIMIT | BAIL_OBJ | BAIL_DEST)) ? COOP_FORCE_B : 0);
+      // own broad + narrow phase over the arm pairs; stage B only for lanes with something to solve
+      LocalSink ks; ks.ncon = 0;
+      if (need && (bail & (BAIL_HAND | BAIL_FOREARM))) fast_arm_collide(c, fo, fd, ks);
+      const bool needB = need && (ks.ncon > 0 || (flags & COOP_FORCE_B));
+      FAST_WSTAT(0);
+      if (need) { FAST_WSTAT(1); if (bail & BAIL_LIMIT) FAST_WSTAT(8); if (bail & (BAIL_HAND | BAIL_FOREARM)) FAST_WSTAT(9); if (bail & (BAIL_OBJ | BAIL_DEST)) FAST_WSTAT(10); }
 #ifdef __CUDA_ARCH__
-      unsigned pending = __ballot_sync(0xffffffffu, need);
+      unsigned pending = __ballot_sync(0xffffffffu, needB);
       const int mylane = threadIdx.x & 31;
       while (pending) {
         const int L = __ffs(pending) - 1; pending &= pending - 1;
-        JPROF_T(t0);
-        if (mylane == L) coop_publish_poses(*ws, c, fo, fd, flags);
-        __syncwarp();
-        const int goB = coop_stageA(*ws);
         JPROF_T(t1);
-        JPROF_ADD(0, 1); JPROF_ADD(1, t1 - t0);
-        if (!goB) continue;
-        if (mylane == L) coop_publish(*ws, s, c, fo, fd, fsm, it == 49);
+        if (mylane == L) { coop_publish(*ws, s, c, fo, fd, fsm, it == 49); coop_publish_contacts(*ws, ks, flags); }
         __syncwarp();
         JPROF_T(t2);
         const int sv = coop_stageB(*ws);
@@ -1008,20 +1095,12 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
         __syncwarp();
       }
 #else
-      FAST_WSTAT(0);
-      if (need) {
-        FAST_WSTAT(1);
-        if (bail & BAIL_LIMIT) FAST_WSTAT(8);
-        if (bail & (BAIL_HAND | BAIL_FOREARM)) FAST_WSTAT(9);
-        if (bail & (BAIL_OBJ | BAIL_DEST)) FAST_WSTAT(10);
-        coop_publish_poses(*ws, c, fo, fd, flags);
-        if (coop_stageA(*ws)) {
-          FAST_WSTAT(2);
-          coop_publish(*ws, s, c, fo, fd, fsm, it == 49);
-          solved = coop_stageB(*ws);
-          if (solved) { FAST_WSTAT(3); FAST_WSTAT_ADD(4, ws->iters); FAST_WSTAT_ADD(5, ws->ncon); if (solved & 1) FAST_WSTAT(6); if (ws->ncon > 0) FAST_WSTAT(7); }
-          if (solved) { for (int i = 0; i < JACO_NV; i++) { qacc_g[i] = ws->qacc[i]; fcon_g[i] = ws->fcon[i]; } if (it == 49) s.touch_now = touch_class(ws->touch); }
-        }
+      if (needB) {
+        FAST_WSTAT(2);
+        coop_publish(*ws, s, c, fo, fd, fsm, it == 49); coop_publish_contacts(*ws, ks, flags);
+        solved = coop_stageB(*ws);
+        if (solved) { FAST_WSTAT(3); FAST_WSTAT_ADD(4, ws->iters); FAST_WSTAT_ADD(5, ws->ncon); if (solved & 1) FAST_WSTAT(6); if (ws->ncon > 0) FAST_WSTAT(7);
+          for (int i = 0; i < JACO_NV; i++) { qacc_g[i] = ws->qacc[i]; fcon_g[i] = ws->fcon[i]; } if (it == 49) s.touch_now = touch_class(ws->touch); }
       }
 #endif
     }

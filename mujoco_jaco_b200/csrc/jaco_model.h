@@ -40,6 +40,7 @@ struct JacoModel {
   float dof_invw[JACO_NV], meaninertia, hand_sphere[4];
   float body_sphere[4][4];  // bounding spheres (body frame: centre xyz, radius) of the collision geoms on bodies 6..9
   float dt, gravz;
+  unsigned long long pm_boxbox, pm_capbox, pm_plane;  // arm pairs (index >= 4) by narrow-phase routine: bit p set
   JacoGeom geoms[JM_NGEOM];
   JacoPair pairs[JM_NPAIR];
   JacoSite sites[JM_NSITE];
@@ -100,6 +101,14 @@ static inline void jaco_model_from_blob(const double* b, JacoModel* m) {
     S->type = (int)r[0]; S->body = (int)r[1]; S->geom = (int)r[17];
     for (int i = 0; i < 3; i++) { S->pos[i] = (float)r[2 + i]; S->size[i] = (float)r[14 + i]; }
     for (int i = 0; i < 9; i++) S->R[i] = (float)r[5 + i];
+  }
+  m->pm_boxbox = m->pm_capbox = m->pm_plane = 0;
+  for (int p = 4; p < JM_NPAIR; p++) {
+    const int t1 = m->geoms[m->pairs[p].g1].type, t2 = m->geoms[m->pairs[p].g2].type;
+    const unsigned long long bit = 1ull << p;
+    if (t1 == JACO_GEOM_PLANE || t2 == JACO_GEOM_PLANE) m->pm_plane |= bit;
+    else if (t1 == JACO_GEOM_BOX && t2 == JACO_GEOM_BOX) m->pm_boxbox |= bit;
+    else m->pm_capbox |= bit;
   }
   // per-body bounding spheres of the hand cluster (hand + three fingers), used by the fast path's proximity tests
   for (int b = 6; b <= 9; b++) {
