@@ -135,6 +135,7 @@ def main():
     import torch.distributed as dist
     from mujoco_jaco_b200 import _lib
     from mujoco_jaco_b200.env import JacoVecEnv, NACT, NOBS
+    from mujoco_jaco_b200.shard import max_over_ranks, reduce_stats, shard_range
 
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -143,7 +144,8 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
     n, K, W = args.envs, args.steps, max(3, args.warmup)
-    env = JacoVecEnv(n, task=args.task, seed=0, device=local, env_offset=rank * n, auto_reset=True)
+    env_offset, _ = shard_range(rank, world, n)   # independent shard of the global env range: no data-path collective
+    env = JacoVecEnv(n, task=args.task, seed=0, device=local, env_offset=env_offset, auto_reset=True)
     env.reset()
     gen = torch.Generator(device=dev); gen.manual_seed(1234 + rank)
     nact = K + W
@@ -173,11 +175,8 @@ def main():
     kernel_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(K)]
     launches = env.launch_count() - launches0
     stats = env.stats(clear=True).clone()
-    t = torch.tensor([total_ms], device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(stats, op=dist.ReduceOp.SUM)   # the only data-path-adjacent collective: episode statistics
-    total_ms = float(t.item())
+    total_ms = max_over_ranks(total_ms, device=dev)   # device time, max over ranks
+    reduce_stats(stats)                                # the only collective of the path: episode statistics (NCCL)
     value = world * n * K / (total_ms * 1e-3)
 
     # ---- e2e through the host-buffer C-ABI call (pinned host buffers, copies inside the timed region)
@@ -194,10 +193,7 @@ def main():
         env.step_host(a_np, outs_np)
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
-    te = torch.tensor([e2e_s], device=dev)
-    if world > 1:
-        dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    e2e_value = world * n * Ke / float(te.item())
+    e2e_value = world * n * Ke / max_over_ranks(e2e_s, device=dev)
     if sampler:
         sampler.stop_flag = True
         sampler.join(timeout=2)

@@ -38,7 +38,9 @@ static __device__ unsigned long long g_jprof[16];
 
 #define COOP_SIMPLE_OBJ 1   // the owner's fast scene collision of the object is valid (it can solve the object alone)
 #define COOP_FORCE_B 2      // active joint limit or non-simple scene contacts: stage B regardless of the arm proximity
+#ifndef COOP_NROW
 #define COOP_NROW 128   // pool of direction-Jacobian rows (3 per condim-3 contact, 6 per condim-6 contact)
+#endif
 
 #if defined(JACO_COLLISION_STATS) && !defined(__CUDACC__)
 static long long g_coop_pairA[64], g_coop_pairC[64];   // CPU harness only: per-pair stage-A survivors / pairs with contacts
@@ -353,6 +355,7 @@ JHD void coop_solve_component(CoopWS& w, int mask) {
   int n = 0, dofs[JACO_NV];
   for (int i = 0; i < JACO_NV; i++) if (coop_block(i) & mask) dofs[n++] = i;
   const int nent = n * (n + 1) / 2;
+  JPROF_T(s0);
   // ---- start point: warm start if it beats qacc_smooth (mj_solNewton warm-start rule)
   float cw_, cs_, t1_, t2_;
   COOP_BEGIN {
@@ -378,7 +381,9 @@ JHD void coop_solve_component(CoopWS& w, int mask) {
     if (usew) { if (c < w.ncon && (w.cmask[c] & mask)) for (int k = 0; k < 6; k++) w.ce[c][k] = w.csc[c][k]; if (lane == 31 && (mask & 1)) for (int r = 0; r < w.nlim; r++) w.le[r] = w.g[r]; }
   } COOP_END
   int iters = 0;
+  JPROF_T(s1); JPROF_ADD(10, s1 - s0);
   for (int it = 0; it < JACO_SOLVER_MAXIT; it++) {
+    JPROF_T(i0);
     // ---- gradient g = M (a - asm) - J^T f
     coop_force(w, mask);
     COOP_BEGIN { int i = lane; if (i < JACO_NV) w.p[i] = (coop_block(i) & mask) ? w.a[i] - w.asm_[i] : 0.0f; } COOP_END
@@ -391,6 +396,7 @@ JHD void coop_solve_component(CoopWS& w, int mask) {
       if (!(gn <= 1e-12f * fn || gn < 1e-20f)) conv = false;
     }
     if (conv) break;
+    JPROF_T(i1); JPROF_ADD(11, i1 - i0);
     // ---- Hessian over the component's dofs
     coop_weights(w, mask);
     COOP_BEGIN {
@@ -422,6 +428,7 @@ JHD void coop_solve_component(CoopWS& w, int mask) {
         w.H[e] = hv;
       }
     } COOP_END
+    JPROF_T(i2); JPROF_ADD(12, i2 - i1);
     // ---- Cholesky (left-looking, lanes over rows), then p = -H^-1 g
     for (int j = 0; j < n; j++) {
       COOP_BEGIN {
@@ -446,6 +453,7 @@ JHD void coop_solve_component(CoopWS& w, int mask) {
     }
     COOP_BEGIN { int i = lane; if (i < JACO_NV) w.p[i] = 0; } COOP_END
     COOP_BEGIN { int k = lane; if (k < n) w.p[dofs[k]] = w.red[k][1]; } COOP_END
+    JPROF_T(i3); JPROF_ADD(13, i3 - i2);
     // ---- exact line search on the piecewise-quadratic phi(al): safeguarded 1-D Newton
     coop_eval(w, mask, w.p, true);
     float q1 = 0, q2 = 0;
@@ -468,6 +476,7 @@ JHD void coop_solve_component(CoopWS& w, int mask) {
       if (nx == al) break;
       al = nx;
     }
+    JPROF_T(i4); JPROF_ADD(14, i4 - i3);
     // ---- update iterate and residuals; per-dof step test
     bool small = true;
     for (int i = 0; i < JACO_NV; i++) if (coop_block(i) & mask) { float st = fabsf(al * w.p[i]); if (!(st <= 2e-7f * fmaxf(1.0f, fabsf(w.a[i] + al * w.p[i])))) small = false; }
@@ -479,6 +488,7 @@ JHD void coop_solve_component(CoopWS& w, int mask) {
       if (lane == 31 && (mask & 1)) for (int r = 0; r < w.nlim; r++) w.le[r] += al * w.lp[r];
     } COOP_END
     iters = it + 1;
+    JPROF_T(i5); JPROF_ADD(15, i5 - i4);
     if (small) break;
   }
   coop_force(w, mask);

@@ -862,6 +862,22 @@ JHD void coop_publish(CoopWS& w, const FastSim& s, const ChainOut& c, const Free
 // Semantics: collide_pair of jaco_sim.cuh in pair order, i.e. exactly what coop_collision would have produced for
 // the candidate pairs; the sink holds at most MAXC arm contacts (the scene contacts of pairs 0..3 come first in
 // the workspace, the total is capped at JACO_MAXCON there).
+// Block-wide re-alignment points of the substep loop (hybrid kernel only).  The substep body is ~24 k straight-line
+// instructions (~380 KB of SASS), far beyond the 32 KB L1.5 instruction cache: warps that run it at different
+// program counters each stream it from L2 on their own (ncu: stall_no_instruction dominates).  Warps of a block that
+// pass these points together share one instruction stream.  JACO_SUBSTEP_SYNC: 0 off, 1 per substep, 2 per phase.
+#ifndef JACO_SUBSTEP_SYNC
+#define JACO_SUBSTEP_SYNC 1
+#endif
+#if defined(__CUDA_ARCH__)
+#define JSYNC1() do { if (COOP && JACO_SUBSTEP_SYNC >= 1) __syncthreads(); } while (0)
+#define JSYNC2() do { if (COOP && JACO_SUBSTEP_SYNC >= 2) __syncthreads(); } while (0)
+#define JSYNC3() do { if (COOP && JACO_SUBSTEP_SYNC >= 3) __syncthreads(); } while (0)
+#else
+#define JSYNC1()
+#define JSYNC2()
+#define JSYNC3()
+#endif
 struct LocalSink {
   static const int MAXC = 24;
   int ncon, cpair[MAXC];
@@ -1016,6 +1032,7 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
   const JacoGeom& GF = m.geoms[FG_FLOOR];
 
   for (int it = 0; it < 50; it++) {
+    JSYNC1();
     // ---- joint limits (mj_instantiateLimit): any active limit row leaves the fast regime
     int bail = 0;
 #pragma unroll
@@ -1024,7 +1041,9 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
     // ---- free boxes at the current state
     FreeBody fo, fd;
     free_body_setup(10, FG_OBJ, s.qpos + 9, s.qvel + 9, fo);
+    JSYNC3();
     free_body_setup(11, FG_DEST, s.qpos + 16, s.qvel + 15, fd);
+    JSYNC3();
     v3copy(s.objp, fo.x);
     v3copy(sb.op, fo.gp); v3copy(sb.dp, fd.gp);
 #pragma unroll
@@ -1045,12 +1064,15 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
       float dd[3]; v3sub(dd, fd.gp, fo.gp);
       if (!(v3norm(dd) > m.geoms[FG_DEST].rbound + m.geoms[FG_OBJ].rbound + m.pairs[FP_DEST_OBJ].margin)) bail |= BAIL_OBJ;
     }
+    JSYNC3();
     fast_plane_box(FP_FLOOR_DEST, GF.pos, GF.R, fd.gp, fd.gR, sb.dh, m.pairs[FP_FLOOR_DEST].margin, cd);
+    JSYNC2();
     // ---- chain dynamics at (q, v), reference point = EE position of the previous forward
     float O[3]; v3copy(O, s.eepos);
     fast_chain<true>(s.qpos, s.qvel, O, &sb, c);
     bail |= c.near;
     if (!COOP && bail) { *why = bail; return FAST_BAIL; }
+    JSYNC2();
     // ---- actuation + smooth forces of the chain (fwd_actuation, mj_passive)
     float fsm[9], acc[9];
     const float gcmd = ramp_value(s, it);
@@ -1104,6 +1126,7 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
       }
 #endif
     }
+    JSYNC2();
     if (it == 49) {  // what the next env step needs from this forward
       if (solved & 1) { for (int i = 0; i < 9; i++) s.warm[i] = qacc_g[i]; }
       else { chain_solve(c, 0.0f, fsm, acc); for (int i = 0; i < 9; i++) s.warm[i] = acc[i]; }
@@ -1113,13 +1136,16 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
     // ---- mj_Euler, chain (implicit joint damping)
     if (solved & 1) { for (int i = 0; i < 9; i++) fsm[i] += fcon_g[i]; }
     if (!chain_solve(c, h, fsm, acc)) { *why = BAIL_NAN; if (!COOP) return FAST_BAIL; dead |= BAIL_NAN; }
+    JSYNC3();
 #pragma unroll
     for (int i = 0; i < 9; i++) { s.qvel[i] += h * acc[i]; s.qpos[i] += h * s.qvel[i]; }
     // ---- free boxes: contact solve + Euler
     if (solved & 2) free_integrate(fo, qacc_g + 9, fcon_g + 9, s.qpos + 9, s.qvel + 9, s.warm + 9);
     else fast_free_step(fo, co, s.qpos + 9, s.qvel + 9, s.warm + 9);
+    JSYNC3();
     if (solved & 4) free_integrate(fd, qacc_g + 15, fcon_g + 15, s.qpos + 16, s.qvel + 15, s.warm + 15);
     else fast_free_step(fd, cd, s.qpos + 16, s.qvel + 15, s.warm + 15);
+    JSYNC2();
     // ---- controller output for the next substep from this forward's mjData and the fresh joint velocity
     v3copy(s.eepos, c.eepos);
 #pragma unroll

@@ -17,4 +17,5 @@ for k in range(6):
     o = out.astype(np.float64)
     print(k, "ms", round(e0.elapsed_time(e1), 2), "stageA calls", int(o[0]), "cyc/call %.0f" % (o[1] / max(o[0], 1)), "| stageB calls", int(o[8]), "publish %.0f" % (o[9] / max(o[8], 1)),
           "stageB %.0f" % (o[2] / max(o[8], 1)), "collision %.0f" % (o[4] / max(o[8], 1)), "constraints %.0f" % (o[5] / max(o[8], 1)), "| solved", int(o[3]),
-          "solve cyc %.0f" % (o[6] / max(o[3], 1)), "iters %.2f" % (o[7] / max(o[3], 1)), flush=True)
+          "solve cyc %.0f" % (o[6] / max(o[3], 1)), "iters %.2f" % (o[7] / max(o[3], 1)),
+          "| per solve: setup %.0f grad %.0f hess %.0f chol %.0f ls %.0f upd %.0f" % tuple(o[10 + k] / max(o[3], 1) for k in range(6)), flush=True)
