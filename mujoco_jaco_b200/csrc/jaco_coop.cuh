@@ -33,6 +33,13 @@ static __device__ unsigned long long g_jprof[16];
 #define COOP_SYNC() ((void)0)
 #define COOP_LANE0
 #endif
+#ifdef __CUDA_ARCH__
+__device__ __forceinline__ float coop_wsum(float v) {   // butterfly sum: every lane gets the same total
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+#endif
 #define COOP_BEGIN COOP_SYNC(); COOP_LANES
 #define COOP_END COOP_SYNC();
 
@@ -126,7 +133,7 @@ JHD int coop_stageA(CoopWS& w) {
 }
 
 // ------------------------------------------------------------------------------------------- collision
-JHD void coop_collision(CoopWS& w) {
+JHD JNOINLINE void coop_collision(CoopWS& w) {
   const JacoModel& m = MDLG;
   float hs[3];
   { float t[3]; m3mulv(t, w.bR[6], m.hand_sphere); v3add(hs, w.bx[6], t); }
@@ -170,7 +177,7 @@ JHD void coop_collision(CoopWS& w) {
 }
 
 // ------------------------------------------------------------------------------------------- constraint rows
-JHD void coop_constraints(CoopWS& w) {
+JHD JNOINLINE void coop_constraints(CoopWS& w) {
   const JacoModel& m = MDLG;
   COOP_SYNC();
   COOP_LANE0 {  // joint limits (mj_instantiateLimit) + row-pool offsets
@@ -252,7 +259,7 @@ JHD void coop_con_cost(const CoopWS& w, int c, float al, float* c0, float* g1, f
   }
 }
 // reduce (cost, d1, d2) of the rows of component `mask` at step al; every lane returns the same totals
-JHD void coop_rows_cost(CoopWS& w, int mask, float al, float* cost, float* d1, float* d2) {
+JHD JNOINLINE void coop_rows_cost(CoopWS& w, int mask, float al, float* cost, float* d1, float* d2) {
   COOP_BEGIN {
     float c0 = 0, g1 = 0, g2 = 0;
     int c = lane;
@@ -263,14 +270,20 @@ JHD void coop_rows_cost(CoopWS& w, int mask, float al, float* cost, float* d1, f
         if (j < 0) { c0 += 0.5f * w.lD[r] * j * j; g1 += w.lD[r] * j * w.lp[r]; g2 += w.lD[r] * w.lp[r] * w.lp[r]; }
       }
     }
+#ifdef __CUDA_ARCH__
+    *cost = coop_wsum(c0); *d1 = coop_wsum(g1); *d2 = coop_wsum(g2);
+#else
     w.red[lane][0] = c0; w.red[lane][1] = g1; w.red[lane][2] = g2;
+#endif
   } COOP_END
+#ifndef __CUDA_ARCH__
   float c0 = 0, g1 = 0, g2 = 0;
   for (int l = 0; l < 32; l++) { c0 += w.red[l][0]; g1 += w.red[l][1]; g2 += w.red[l][2]; }
   *cost = c0; *d1 = g1; *d2 = g2;
+#endif
 }
 // component Jacobian times a workspace vector x: into ce (minus aref) or cp
-JHD void coop_eval(CoopWS& w, int mask, const float* x, bool is_dir) {
+JHD JNOINLINE void coop_eval(CoopWS& w, int mask, const float* x, bool is_dir) {
   COOP_BEGIN {
     for (int t = lane; t < w.ncon * 6; t += 32) {
       int c = t / 6, d = t - 6 * c;
@@ -295,7 +308,7 @@ JHD float coop_mul_M_row(const CoopWS& w, int i, const float* x) {
   return a;
 }
 // comps-space forces of every contact of the component (rows_force), then jf = J^T f by dof
-JHD void coop_force(CoopWS& w, int mask) {
+JHD JNOINLINE void coop_force(CoopWS& w, int mask) {
   COOP_BEGIN {
     int c = lane;
     if (c < w.ncon && (w.cmask[c] & mask)) {
@@ -329,7 +342,7 @@ JHD void coop_force(CoopWS& w, int mask) {
   } COOP_END
 }
 // comps-space Hessian weights of each contact: cW = {w00, w0k (k=1..5), wkk (k=1..5)}
-JHD void coop_weights(CoopWS& w, int mask) {
+JHD JNOINLINE void coop_weights(CoopWS& w, int mask) {
   COOP_BEGIN {
     int c = lane;
     if (c < w.ncon && (w.cmask[c] & mask)) {
@@ -347,10 +360,113 @@ JHD void coop_weights(CoopWS& w, int mask) {
   } COOP_END
 }
 
+// ------------------------------------------------------------------------------------------- device-only warp primitives
+#ifdef __CUDA_ARCH__
+// Newton direction p = -H^-1 g of component `mask`, H = M + J^T W J held in registers: lane l owns column l of the
+// (symmetric) 21 x 21 Hessian, dofs outside the component are identity rows.  Assembly reads the direction
+// Jacobians from the workspace (broadcast loads), the Cholesky factorisation is right-looking with one shuffle per
+// rank-1 term, the two triangular solves exchange the factor through w.H.  Same arithmetic as the portable path
+// below (coop_solve_component, CPU harness) up to summation order.
+__device__ __noinline__ void coop_newton_dir_dev(CoopWS& w, int mask) {
+  const int lane = threadIdx.x & 31;
+  const int j = lane < JACO_NV ? lane : JACO_NV - 1;          // lanes >= 21 shadow dof 20 (never stored)
+  const int bj = coop_block(j);
+  const bool inb = (bj & mask) != 0;
+  float h[JACO_NV];
+#pragma unroll
+  for (int i = 0; i < JACO_NV; i++) {
+    float v = 0;
+    const int bi = coop_block(i);
+    if (inb && bi == bj) {
+      if (i < 9) v = w.Mc[i >= j ? PK(i, j) : PK(j, i)];
+      else { const int f = (i - 9) / 6, a = i - 9 - 6 * f, b = j - 9 - 6 * f; v = w.Mf[f][a >= b ? PK(a, b) : PK(b, a)]; }
+    }
+    if (!inb && i == j) v = 1.0f;
+    h[i] = v;
+  }
+  if (mask & 1) {
+    float add = 0;
+    for (int r = 0; r < w.nlim; r++) if (w.ldof[r] == j && w.le[r] < 0) add += w.lD[r];
+#pragma unroll
+    for (int i = 0; i < 9; i++) if (i == j) h[i] += add;
+  }
+  for (int c = 0; c < w.ncon; c++) {
+    if (!(w.cmask[c] & mask)) continue;
+    const float* W = w.cW[c];
+    const int r0 = w.croff[c], condim = w.ccond[c];
+    const float J0 = w.Jd[r0][j];
+    float T0 = W[0] * J0, Tk[5];
+#pragma unroll
+    for (int k = 1; k < 6; k++) {
+      float t = 0;
+      if (k < condim) { const float Jk = w.Jd[r0 + k][j]; T0 += W[k] * Jk; t = W[k] * J0 + W[5 + k] * Jk; }
+      Tk[k - 1] = t;
+    }
+    if (condim <= 3) {
+#pragma unroll
+      for (int i = 0; i < JACO_NV; i++) {
+        float a = w.Jd[r0][i] * T0;
+        if (condim == 3) { a += w.Jd[r0 + 1][i] * Tk[0]; a += w.Jd[r0 + 2][i] * Tk[1]; }
+        h[i] += a;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < JACO_NV; i++) {
+        float a = w.Jd[r0][i] * T0;
+#pragma unroll
+        for (int k = 1; k < 6; k++) a += w.Jd[r0 + k][i] * Tk[k - 1];
+        h[i] += a;
+      }
+    }
+  }
+  if (!inb) {   // keep excluded dofs exactly decoupled (their Jacobian entries are zero, this guards rounding paths)
+#pragma unroll
+    for (int i = 0; i < JACO_NV; i++) h[i] = (i == j) ? 1.0f : 0.0f;
+  }
+  // ---- right-looking Cholesky: after step c, h[c] of lane l >= c holds L[l][c]
+#pragma unroll
+  for (int c = 0; c < JACO_NV; c++) {
+    float d = __shfl_sync(0xffffffffu, h[c], c);
+    if (!(d > 0)) d = 1;
+    const float ir = rsqrtf(d);
+    const float lc = (lane == c) ? d * ir : h[c] * ir;
+    h[c] = lc;
+#pragma unroll
+    for (int k = c + 1; k < JACO_NV; k++) {
+      const float lk = __shfl_sync(0xffffffffu, lc, k);   // L[k][c]
+      h[k] -= lc * lk;                                   // lane l: H[k][l] -= L[l][c] L[k][c]  (used for l >= k)
+    }
+  }
+  // ---- L y = -g (column oriented), then L^T x = y with the factor's rows read back from the workspace
+  float b = (lane < JACO_NV && inb) ? -w.g[lane] : 0.0f;
+  float dinv = 1.0f;
+#pragma unroll
+  for (int c = 0; c < JACO_NV; c++) if (c == j) dinv = 1.0f / h[c];
+#pragma unroll
+  for (int c = 0; c < JACO_NV; c++) {
+    const float yc = __shfl_sync(0xffffffffu, b * dinv, c);
+    if (lane == c) b = yc; else if (lane > c) b -= h[c] * yc;
+  }
+  if (lane < JACO_NV) {
+#pragma unroll
+    for (int c = 0; c < JACO_NV; c++) if (c <= lane) w.H[PK(lane, c)] = h[c];
+  }
+  __syncwarp();
+#pragma unroll
+  for (int c = JACO_NV - 1; c >= 0; c--) {
+    const float xc = __shfl_sync(0xffffffffu, b * dinv, c);
+    if (lane == c) b = xc; else if (lane < c) b -= w.H[PK(c, j)] * xc;   // L[c][lane]
+  }
+  __syncwarp();
+  if (lane < JACO_NV) w.p[lane] = inb ? b : 0.0f;
+  __syncwarp();
+}
+#endif
+
 // ------------------------------------------------------------------------------------------- Newton per component
 // Solves the rows of the blocks in `mask` (bit 1 chain, 2 object, 4 dest) jointly; w.a holds the iterate (all 21
 // entries; blocks outside `mask` are not touched).
-JHD void coop_solve_component(CoopWS& w, int mask) {
+JHD JNOINLINE void coop_solve_component(CoopWS& w, int mask) {
   // compact dof list of the component
   int n = 0, dofs[JACO_NV];
   for (int i = 0; i < JACO_NV; i++) if (coop_block(i) & mask) dofs[n++] = i;
@@ -389,16 +505,34 @@ JHD void coop_solve_component(CoopWS& w, int mask) {
     COOP_BEGIN { int i = lane; if (i < JACO_NV) w.p[i] = (coop_block(i) & mask) ? w.a[i] - w.asm_[i] : 0.0f; } COOP_END
     COOP_BEGIN { int i = lane; if (i < JACO_NV) { float md = (coop_block(i) & mask) ? coop_mul_M_row(w, i, w.p) : 0.0f; w.Mp[i] = md; w.g[i] = md - w.jf[i]; } } COOP_END
     bool conv = true;  // block-wise relative gradient test (each block against its own force scale)
+#ifdef __CUDA_ARCH__
+    {
+      const int ln = threadIdx.x & 31;
+      const bool v = ln < JACO_NV;
+      const int bl = v ? coop_block(ln) : 0;
+      const float gi = v ? w.g[ln] * w.g[ln] : 0.0f, fi = v ? w.jf[ln] * w.jf[ln] + w.Mp[ln] * w.Mp[ln] : 0.0f;
+      for (int b = 1; b <= 4; b <<= 1) {
+        if (!(mask & b)) continue;
+        const float gn = coop_wsum(bl == b ? gi : 0.0f), fn = coop_wsum(bl == b ? fi : 0.0f);
+        if (!(gn <= 1e-12f * fn || gn < 1e-20f)) conv = false;
+      }
+    }
+#else
     for (int b = 1; b <= 4; b <<= 1) {
       if (!(mask & b)) continue;
       float gn = 0, fn = 0;
       for (int i = 0; i < JACO_NV; i++) if (coop_block(i) == b) { fn += w.jf[i] * w.jf[i] + w.Mp[i] * w.Mp[i]; gn += w.g[i] * w.g[i]; }
       if (!(gn <= 1e-12f * fn || gn < 1e-20f)) conv = false;
     }
+#endif
     if (conv) break;
     JPROF_T(i1); JPROF_ADD(11, i1 - i0);
     // ---- Hessian over the component's dofs
     coop_weights(w, mask);
+#ifdef __CUDA_ARCH__
+    coop_newton_dir_dev(w, mask);
+    JPROF_T(i2); JPROF_ADD(12, i2 - i1);
+#else
     COOP_BEGIN {
       for (int e = lane; e < nent; e += 32) {
         int ci = 0; while ((ci + 1) * (ci + 2) / 2 <= e) ci++;
@@ -428,7 +562,6 @@ JHD void coop_solve_component(CoopWS& w, int mask) {
         w.H[e] = hv;
       }
     } COOP_END
-    JPROF_T(i2); JPROF_ADD(12, i2 - i1);
     // ---- Cholesky (left-looking, lanes over rows), then p = -H^-1 g
     for (int j = 0; j < n; j++) {
       COOP_BEGIN {
@@ -453,13 +586,21 @@ JHD void coop_solve_component(CoopWS& w, int mask) {
     }
     COOP_BEGIN { int i = lane; if (i < JACO_NV) w.p[i] = 0; } COOP_END
     COOP_BEGIN { int k = lane; if (k < n) w.p[dofs[k]] = w.red[k][1]; } COOP_END
+#endif
     JPROF_T(i3); JPROF_ADD(13, i3 - i2);
     // ---- exact line search on the piecewise-quadratic phi(al): safeguarded 1-D Newton
     coop_eval(w, mask, w.p, true);
     float q1 = 0, q2 = 0;
     {  // Mp currently holds M (a - asm); q1 = p . M d, q2 = p . M p
+#ifdef __CUDA_ARCH__
+      const int ln = threadIdx.x & 31;
+      float mp = 0, pi = 0, mdi = 0;
+      if (ln < JACO_NV && (coop_block(ln) & mask)) { mp = coop_mul_M_row(w, ln, w.p); pi = w.p[ln]; mdi = w.Mp[ln]; }
+      q2 = coop_wsum(pi * mp); q1 = coop_wsum(pi * mdi);
+#else
       COOP_BEGIN { int i = lane; if (i < JACO_NV) { w.red[i][2] = (coop_block(i) & mask) ? coop_mul_M_row(w, i, w.p) : 0.0f; } } COOP_END
       for (int i = 0; i < JACO_NV; i++) { q2 += w.p[i] * w.red[i][2]; q1 += w.p[i] * w.Mp[i]; }
+#endif
     }
     float lo = 0, hi = -1, al = 0, d1, d2, c0;
     coop_rows_cost(w, mask, 0.0f, &c0, &d1, &d2);
@@ -479,7 +620,16 @@ JHD void coop_solve_component(CoopWS& w, int mask) {
     JPROF_T(i4); JPROF_ADD(14, i4 - i3);
     // ---- update iterate and residuals; per-dof step test
     bool small = true;
+#ifdef __CUDA_ARCH__
+    {
+      const int ln = threadIdx.x & 31;
+      bool ok = true;
+      if (ln < JACO_NV && (coop_block(ln) & mask)) { float st = fabsf(al * w.p[ln]); ok = st <= 2e-7f * fmaxf(1.0f, fabsf(w.a[ln] + al * w.p[ln])); }
+      small = __all_sync(0xffffffffu, ok);
+    }
+#else
     for (int i = 0; i < JACO_NV; i++) if (coop_block(i) & mask) { float st = fabsf(al * w.p[i]); if (!(st <= 2e-7f * fmaxf(1.0f, fabsf(w.a[i] + al * w.p[i])))) small = false; }
+#endif
     COOP_BEGIN {
       int i = lane;
       if (i < JACO_NV && (coop_block(i) & mask)) w.a[i] += al * w.p[i];
@@ -496,7 +646,7 @@ JHD void coop_solve_component(CoopWS& w, int mask) {
 }
 
 // ------------------------------------------------------------------------------------------- touch sensors
-JHD void coop_touch(CoopWS& w) {
+JHD JNOINLINE void coop_touch(CoopWS& w) {
   const JacoModel& m = MDLG;
   COOP_BEGIN {
     int k = lane;

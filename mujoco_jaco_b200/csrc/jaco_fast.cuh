@@ -867,7 +867,7 @@ JHD void coop_publish(CoopWS& w, const FastSim& s, const ChainOut& c, const Free
 // program counters each stream it from L2 on their own (ncu: stall_no_instruction dominates).  Warps of a block that
 // pass these points together share one instruction stream.  JACO_SUBSTEP_SYNC: 0 off, 1 per substep, 2 per phase.
 #ifndef JACO_SUBSTEP_SYNC
-#define JACO_SUBSTEP_SYNC 1
+#define JACO_SUBSTEP_SYNC 2
 #endif
 #if defined(__CUDA_ARCH__)
 #define JSYNC1() do { if (COOP && JACO_SUBSTEP_SYNC >= 1) __syncthreads(); } while (0)
@@ -877,6 +877,9 @@ JHD void coop_publish(CoopWS& w, const FastSim& s, const ChainOut& c, const Free
 #define JSYNC1()
 #define JSYNC2()
 #define JSYNC3()
+#endif
+#ifndef JACO_TIMING_SKIP   /* timing experiments only (scripts/build_variant.sh): bit 0 no stage B, bit 1 no arm collision, bit 2 arm stage A only */
+#define JACO_TIMING_SKIP 0
 #endif
 struct LocalSink {
   static const int MAXC = 24;
@@ -888,40 +891,87 @@ struct LocalPoses {
   const float* bx[JACO_NBODY];
   const float* bR[JACO_NBODY];
 };
-#ifdef __CUDACC__
-#define JNOINLINE __noinline__
-#else
-#define JNOINLINE __attribute__((noinline))
-#endif
 JHD JNOINLINE void fast_arm_collide(const ChainOut& c, const FreeBody& fo, const FreeBody& fd, LocalSink& k) {
   const JacoModel& m = MDL;
   const float Z3[3] = {0, 0, 0}, I9[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+  k.ncon = 0;
+  // world pose of the four scene geoms (0 floor, 1 holder, 2 object, 3 dest)
+  float sp[4][3], sR[4][9];
+#pragma unroll
+  for (int g = 0; g < 2; g++) { v3copy(sp[g], m.geoms[g].pos);
+#pragma unroll
+    for (int i = 0; i < 9; i++) sR[g][i] = m.geoms[g].R[i]; }
+  v3copy(sp[2], fo.gp); v3copy(sp[3], fd.gp);
+#pragma unroll
+  for (int i = 0; i < 9; i++) { sR[2][i] = fo.gR[i]; sR[3][i] = fd.gR[i]; }
+  // ---- stage A (uniform loop over the arm pairs: constant-bank reads).  Level 1: bounding sphere of the arm geom
+  // against the exact scene box / plane.  Level 2, conservative and cheap: separating face axes (box-box), the
+  // capsule's bounding box in the scene-box frame (capsule-box), the exact lowest point (plane-capsule).
+  unsigned long long cand = 0;
+  for (int p = 4; p < JM_NPAIR; p++) {
+    const JacoPair& P = m.pairs[p];
+    const bool arm1 = P.g1 > 3;
+    const JacoGeom& A = arm1 ? m.geoms[P.g1] : m.geoms[P.g2];
+    const int sg = arm1 ? P.g2 : P.g1;
+    const JacoGeom& S = m.geoms[sg];
+    const float* bR = c.bRm[A.body - 3];
+    float cc[3], t[3], d[3], l[3];
+    m3mulv(t, bR, A.pos); v3add(cc, c.bp[A.body - 3], t);
+    const float rr = A.rbound + P.margin + 1e-5f;
+    v3sub(d, cc, sp[sg]); m3tmulv(l, sR[sg], d);             // arm geom centre in the scene geom's frame
+    bool hit;
+    if (S.type == JACO_GEOM_PLANE) {
+      hit = !(l[2] > rr);
+      if (hit && A.type == JACO_GEOM_CAPSULE) {
+        float ax[3], ga[3] = {A.R[2], A.R[5], A.R[8]}; m3mulv(ax, bR, ga);
+        const float az = sR[sg][2] * ax[0] + sR[sg][5] * ax[1] + sR[sg][8] * ax[2];
+        hit = !(l[2] - fabsf(az) * A.size[1] - A.size[0] > P.margin + 1e-5f);
+      }
+    } else {
+      const float e0 = fmaxf(fabsf(l[0]) - S.size[0], 0.0f), e1 = fmaxf(fabsf(l[1]) - S.size[1], 0.0f), e2 = fmaxf(fabsf(l[2]) - S.size[2], 0.0f);
+      hit = !(e0 * e0 + e1 * e1 + e2 * e2 > rr * rr);
+      if (hit && A.type == JACO_GEOM_CAPSULE) {
+        float ax[3], al[3], ga[3] = {A.R[2], A.R[5], A.R[8]}; m3mulv(ax, bR, ga); m3tmulv(al, sR[sg], ax);
+        const float hl = A.size[1], r2 = A.size[0] + P.margin + 1e-5f;
+        const float g0 = fmaxf(fabsf(l[0]) - hl * fabsf(al[0]) - S.size[0], 0.0f), g1 = fmaxf(fabsf(l[1]) - hl * fabsf(al[1]) - S.size[1], 0.0f),
+                    g2 = fmaxf(fabsf(l[2]) - hl * fabsf(al[2]) - S.size[2], 0.0f);
+        hit = !(g0 * g0 + g1 * g1 + g2 * g2 > r2 * r2);
+      } else if (hit && A.type == JACO_GEOM_BOX) {
+        float Ra[9], C[9];                                     // C = Rs^T Ra: arm box axes in the scene box frame
+        m3mul(Ra, bR, A.R);
+#pragma unroll
+        for (int i = 0; i < 3; i++)
+#pragma unroll
+          for (int j = 0; j < 3; j++) C[3 * i + j] = sR[sg][i] * Ra[j] + sR[sg][3 + i] * Ra[3 + j] + sR[sg][6 + i] * Ra[6 + j];
+        const float mg = P.margin + 1e-5f;
+        bool sep = false;
+#pragma unroll
+        for (int i = 0; i < 3; i++) {   // scene box face axes
+          const float ra = A.size[0] * fabsf(C[3 * i]) + A.size[1] * fabsf(C[3 * i + 1]) + A.size[2] * fabsf(C[3 * i + 2]);
+          sep = sep || (fabsf(l[i]) - S.size[i] - ra > mg);
+        }
+#pragma unroll
+        for (int j = 0; j < 3; j++) {   // arm box face axes
+          const float la = l[0] * C[j] + l[1] * C[3 + j] + l[2] * C[6 + j];
+          const float rb = S.size[0] * fabsf(C[j]) + S.size[1] * fabsf(C[3 + j]) + S.size[2] * fabsf(C[6 + j]);
+          sep = sep || (fabsf(la) - A.size[j] - rb > mg);
+        }
+        hit = !sep;
+      }
+    }
+    if (hit) cand |= 1ull << p;
+  }
+  FAST_WSTAT(11);
+  if (cand) FAST_WSTAT(12);
+  if (!cand) return;
+  if (JACO_TIMING_SKIP & 4) { k.ncon = (int)(cand >> 63); return; }
+  // ---- narrow phase, one routine at a time so that lanes working on different pairs stay converged
   LocalPoses ps;
   ps.bx[0] = Z3; ps.bR[0] = I9;
   ps.bx[1] = ps.bx[2] = Z3; ps.bR[1] = ps.bR[2] = I9;   // bodies 1, 2 carry no collision geoms
 #pragma unroll
   for (int b = 3; b <= 9; b++) { ps.bx[b] = c.bp[b - 3]; ps.bR[b] = c.bRm[b - 3]; }
   ps.bx[10] = fo.x; ps.bR[10] = fo.R; ps.bx[11] = fd.x; ps.bR[11] = fd.R;
-  k.ncon = 0;
-  // ---- stage A: bounding sphere of the arm geom against the exact scene box / plane (uniform loop: constant-bank reads)
-  unsigned long long cand = 0;
-  for (int p = 4; p < JM_NPAIR; p++) {
-    const JacoPair& P = m.pairs[p];
-    const bool arm1 = m.geoms[P.g1].body >= 1 && m.geoms[P.g1].body <= 9;
-    const JacoGeom& A = arm1 ? m.geoms[P.g1] : m.geoms[P.g2];
-    const JacoGeom& S = arm1 ? m.geoms[P.g2] : m.geoms[P.g1];
-    float cc[3], t[3], sp[3], R[9];
-    m3mulv(t, ps.bR[A.body], A.pos); v3add(cc, ps.bx[A.body], t);
-    const float rr = A.rbound + P.margin + 1e-5f;
-    m3mulv(t, ps.bR[S.body], S.pos); v3add(sp, ps.bx[S.body], t); m3mul(R, ps.bR[S.body], S.R);
-    bool hit;
-    if (S.type == JACO_GEOM_PLANE) { float d[3]; v3sub(d, cc, sp); hit = !(d[0] * R[2] + d[1] * R[5] + d[2] * R[8] > rr); }
-    else if (S.type == JACO_GEOM_BOX) hit = !(point_box_dist2(cc, sp, R, S.size) > rr * rr);
-    else hit = true;
-    if (hit) cand |= 1ull << p;
-  }
-  if (!cand) return;
-  // ---- narrow phase, one routine at a time so that lanes working on different pairs stay converged
   float hs[3];
   { float t[3]; m3mulv(t, ps.bR[6], m.hand_sphere); v3add(hs, ps.bx[6], t); }
   // contacts must come out in pair order: collect per routine, then merge by pair index
@@ -947,6 +997,7 @@ JHD JNOINLINE void fast_arm_collide(const ChainOut& c, const FreeBody& fo, const
       v3copy(k.cpos[d], tmp.cpos[j]); v3copy(k.cn[d], tmp.cn[j]); k.cdist[d] = tmp.cdist[j]; k.cpair[d] = p;
     }
   }
+  if (k.ncon) FAST_WSTAT(13);
 }
 
 // Owner thread -> warp workspace: its pre-collided arm contacts; stage B then runs its narrow phase on the scene
@@ -1093,8 +1144,8 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
       const int flags = ((bail & (BAIL_OBJ | BAIL_DEST)) ? 0 : COOP_SIMPLE_OBJ) | ((bail & (BAIL_LIMIT | BAIL_OBJ | BAIL_DEST)) ? COOP_FORCE_B : 0);
       // own broad + narrow phase over the arm pairs; stage B only for lanes with something to solve
       LocalSink ks; ks.ncon = 0;
-      if (need && (bail & (BAIL_HAND | BAIL_FOREARM))) fast_arm_collide(c, fo, fd, ks);
-      const bool needB = need && (ks.ncon > 0 || (flags & COOP_FORCE_B));
+      if (!(JACO_TIMING_SKIP & 2) && need && (bail & (BAIL_HAND | BAIL_FOREARM))) fast_arm_collide(c, fo, fd, ks);
+      const bool needB = !(JACO_TIMING_SKIP & 1) && need && (ks.ncon > 0 || (flags & COOP_FORCE_B));
       FAST_WSTAT(0);
       if (need) { FAST_WSTAT(1); if (bail & BAIL_LIMIT) FAST_WSTAT(8); if (bail & (BAIL_HAND | BAIL_FOREARM)) FAST_WSTAT(9); if (bail & (BAIL_OBJ | BAIL_DEST)) FAST_WSTAT(10); }
 #ifdef __CUDA_ARCH__

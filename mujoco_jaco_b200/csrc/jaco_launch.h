@@ -6,7 +6,7 @@
 #include "jaco_fast.cuh"
 
 #ifndef JACO_FAST_BLOCK
-#define JACO_FAST_BLOCK 128
+#define JACO_FAST_BLOCK 256   // one 8-warp block per SM at 255 registers: all resident warps share one instruction stream
 #endif
 #ifndef JACO_FAST_MINBLOCKS
 #define JACO_FAST_MINBLOCKS 1

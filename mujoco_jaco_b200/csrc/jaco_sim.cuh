@@ -14,10 +14,12 @@
 
 #ifdef __CUDACC__
 #define JHD __host__ __device__ inline
+#define JNOINLINE __noinline__   // cold / shared helpers: one copy of the code (instruction-cache footprint), ABI call
 static __constant__ JacoModel c_jaco_model;   // uniform (same address in every lane) accesses: the per-thread paths
 static __device__ JacoModel g_jaco_model_dev; // lane-varying accesses (pairs / geoms indexed by lane): the cooperative path
 #else
 #define JHD inline
+#define JNOINLINE __attribute__((noinline))
 #endif
 static JacoModel g_jaco_model_host;
 #ifdef __CUDA_ARCH__

@@ -13,7 +13,7 @@ sim = HostSim(n, task="picking", seed=0)
 sim.reset()
 rng = np.random.default_rng(0)
 out = np.zeros(16, np.int64)
-names = ["substeps", "need", "stageB", "solved", "iters", "ncon", "solved_chain", "solved_withcon", "limit", "armprox", "objdest"]
+names = ["substeps", "need", "stageB", "solved", "iters", "ncon", "solved_chain", "solved_withcon", "limit", "armprox", "objdest", "armcollide", "narrow", "armcontacts"]
 for k in range(steps):
     a = rng.uniform(-1, 1, (n, 7)).astype(np.float32)
     o, r, d, s, wb, why = sim.step_fast(a, auto_reset=True, allow_fallback=2)
