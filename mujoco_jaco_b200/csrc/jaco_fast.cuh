@@ -907,12 +907,45 @@ JHD JNOINLINE void fast_arm_collide(const ChainOut& c, const FreeBody& fo, const
   // ---- stage A (uniform loop over the arm pairs: constant-bank reads).  Level 1: bounding sphere of the arm geom
   // against the exact scene box / plane.  Level 2, conservative and cheap: separating face axes (box-box), the
   // capsule's bounding box in the scene-box frame (capsule-box), the exact lowest point (plane-capsule).
+  // Level 0: (arm body, scene geom) combinations whose body bounding sphere reaches the scene geom; bit 4 * (body - 3)
+  // + scene.  The fore-arm bodies 3..5 carry one capsule each and are always kept.
+  unsigned nearbits = 0xFFFu;
+#pragma unroll
+  for (int j = 0; j < 4; j++) {
+    const float* BS = m.body_sphere[j];
+    float cc[3], t[3];
+    m3mulv(t, c.bRm[3 + j], BS); v3add(cc, c.bp[3 + j], t);
+    const float rr = BS[3] + 1e-5f;
+#pragma unroll
+    for (int g = 0; g < 4; g++) {
+      float d[3], l[3];
+      v3sub(d, cc, sp[g]); m3tmulv(l, sR[g], d);
+      bool hit;
+      if (g == 0) hit = !(l[2] > rr);
+      else {
+        const float* hsz = m.geoms[g].size;
+        const float e0 = fmaxf(fabsf(l[0]) - hsz[0], 0.0f), e1 = fmaxf(fabsf(l[1]) - hsz[1], 0.0f), e2 = fmaxf(fabsf(l[2]) - hsz[2], 0.0f);
+        hit = !(e0 * e0 + e1 * e1 + e2 * e2 > rr * rr);
+      }
+      if (hit) nearbits |= 1u << (4 * (3 + j) + g);
+    }
+  }
+#ifdef __CUDA_ARCH__
+  unsigned warpbits = nearbits;   // union over the lanes that are in here together: keeps the pair loop uniform
+  { const unsigned am = __activemask();
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) warpbits |= __shfl_xor_sync(am, warpbits, o) ; }
+#else
+  const unsigned warpbits = nearbits;
+#endif
   unsigned long long cand = 0;
   for (int p = 4; p < JM_NPAIR; p++) {
     const JacoPair& P = m.pairs[p];
     const bool arm1 = P.g1 > 3;
     const JacoGeom& A = arm1 ? m.geoms[P.g1] : m.geoms[P.g2];
     const int sg = arm1 ? P.g2 : P.g1;
+    if (!((warpbits >> (4 * (A.body - 3) + sg)) & 1u)) continue;   // uniform skip
+    if (!((nearbits >> (4 * (A.body - 3) + sg)) & 1u)) continue;
     const JacoGeom& S = m.geoms[sg];
     const float* bR = c.bRm[A.body - 3];
     float cc[3], t[3], d[3], l[3];
