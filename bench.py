@@ -29,6 +29,15 @@ ALG_BYTES_PER_ENVSTEP = 2 * (23 + 21 + 72) * 4 + 28 + 104 + 4 + 4 + 1 + 1
 ALG_FLOPS_PER_ENVSTEP = float(os.environ.get("JACO_FLOPS_PER_ENVSTEP", 1.9e6))
 
 
+def _ncu_traffic():
+    """dram bytes (read + write) per launch of the step kernel from the committed ncu --set full summary, or None."""
+    p = os.path.join(REPO, "profiles", "r01_ncu_step_kernel.json")
+    try:
+        return json.load(open(p)).get("dram_bytes_per_launch")
+    except Exception:
+        return None
+
+
 def _peaks():
     p = os.path.join(REPO, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -124,6 +133,9 @@ def main():
     ap.add_argument("--envs", type=int, default=65536, help="envs per GPU (BASELINE config 3: 65536)")
     ap.add_argument("--task", default="picking")
     ap.add_argument("--impl", default="b200")
+    ap.add_argument("--age-steps", type=int, default=200,
+                    help="untimed roll-out steps before the warm-up (SURVEY 8d C3: 200): the workload drifts as episodes age "
+                         "(more arm-scene contacts), so timing straight after reset() would measure an easier mix")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -141,6 +153,7 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # stdout carries exactly one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
     n, K, W = args.envs, args.steps, max(3, args.warmup)
@@ -157,6 +170,8 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
+    for i in range(args.age_steps):
+        env.step(actions[i % actions.shape[0]])
     for i in range(W):
         env.step(actions[i % actions.shape[0]])
     env.stats(clear=True)
@@ -164,15 +179,20 @@ def main():
     if sampler:
         sampler.start()
     launches0 = env.launch_count()
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(K + 1)]
+    # L2 is flushed between timed iterations (a 256 MB fill, outside the per-step event pairs): the state working set
+    # (30 MB) would otherwise stay resident in the 126 MB L2 from one step to the next
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    ev0 = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+    ev1 = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
     barrier()
-    ev[0].record()
     for i in range(K):
+        flush.fill_(i & 255)
+        ev0[i].record()
         env.step(actions[(W + i) % actions.shape[0]])
-        ev[i + 1].record()
+        ev1[i].record()
     barrier()
-    total_ms = ev[0].elapsed_time(ev[K])
-    kernel_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(K)]
+    kernel_ms = [ev0[i].elapsed_time(ev1[i]) for i in range(K)]
+    total_ms = sum(kernel_ms)
     launches = env.launch_count() - launches0
     stats = env.stats(clear=True).clone()
     total_ms = max_over_ranks(total_ms, device=dev)   # device time, max over ranks
@@ -181,16 +201,16 @@ def main():
 
     # ---- e2e through the host-buffer C-ABI call (pinned host buffers, copies inside the timed region)
     Ke = max(3, min(K, 10))
-    a_host = torch.empty(n, NACT).uniform_(-1, 1).pin_memory()
+    a_hosts = [torch.empty(n, NACT).uniform_(-1, 1).pin_memory() for _ in range(8)]   # fresh actions every step
     outs = (torch.empty(n, NOBS).pin_memory(), torch.empty(n).pin_memory(), torch.empty(n, dtype=torch.uint8).pin_memory(),
             torch.empty(n, dtype=torch.uint8).pin_memory(), torch.empty(n).pin_memory())
     outs_np = tuple(o.numpy() for o in outs)
-    a_np = a_host.numpy()
-    env.step_host(a_np, outs_np)
+    a_nps = [a.numpy() for a in a_hosts]
+    env.step_host(a_nps[-1], outs_np)
     barrier()
     t0 = time.perf_counter()
     for i in range(Ke):
-        env.step_host(a_np, outs_np)
+        env.step_host(a_nps[i % len(a_nps)], outs_np)
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     e2e_value = world * n * Ke / max_over_ranks(e2e_s, device=dev)
@@ -213,13 +233,15 @@ def main():
             "config": {"workload": f"batched {args.task} with finger-object contacts: {n} envs per GPU (BASELINE config 3), "
                                    "reset distribution, actions U(-1,1)^7, auto-reset, 50 substeps x 1 ms per step",
                        "envs_per_gpu": n, "substeps_per_step": 50,
-                       "l2": f"state working set {116 * 4 * n / 1e6:.0f} MB SoA + per-thread scratch; inputs > L2 not applicable: "
-                             "compute-bound kernel, fresh actions each step"},
+                       "episode_age": f"{args.age_steps} untimed roll-out steps after reset() before the {W} warm-up steps "
+                                      "(step time grows with episode age, profiles/r01_step_time_trend.log)",
+                       "l2": "flushed between timed iterations (256 MB fill outside the per-step CUDA-event pairs; "
+                             f"state working set {116 * 4 * n / 1e6:.0f} MB)"},
             "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": n * NACT * 4,
                     "d2h_bytes_per_step": n * (NOBS * 4 + 4 + 4 + 1 + 1), "steps": Ke},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": hbm_ach, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                         "frac": hbm_ach / peaks["hbm_gbs"], "traffic": None, "peak_source": which,
+                         "frac": hbm_ach / peaks["hbm_gbs"], "traffic": _ncu_traffic() if n == 65536 else None, "peak_source": which,
                          "note": "HBM is not the limiter of this kernel (50 substeps fused per state round trip); see fp32"},
             "roofline_fp32": {"bound": "fp32", "achieved": fl_ach, "peak": fp32_peak, "unit": "TFLOP/s",
                               "frac": fl_ach / fp32_peak if fp32_peak > 0 else None,
