@@ -85,6 +85,7 @@ struct CoopWS {
   // ---- results
   float qacc[JACO_NV], fcon[JACO_NV], touch[20];
   int iters;
+  int solved;   // stage-B result (block mask) for the owner thread, which may sit in another warp (block task queue)
 };
 
 JHD int coop_ndir(int condim) { return condim <= 3 ? (condim == 1 ? 1 : 3) : 6; }

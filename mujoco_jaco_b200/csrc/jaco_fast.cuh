@@ -891,7 +891,9 @@ struct LocalPoses {
   const float* bx[JACO_NBODY];
   const float* bR[JACO_NBODY];
 };
-JHD JNOINLINE void fast_arm_collide(const ChainOut& c, const FreeBody& fo, const FreeBody& fd, LocalSink& k) {
+// cand_out != nullptr: stop after stage A and return the candidate-pair mask (the device path hands the narrow phase
+// to the block's collision queue); nullptr: also run the narrow phase here (CPU harness, same contacts).
+JHD JNOINLINE void fast_arm_collide(const ChainOut& c, const FreeBody& fo, const FreeBody& fd, LocalSink& k, unsigned long long* cand_out = nullptr) {
   const JacoModel& m = MDL;
   const float Z3[3] = {0, 0, 0}, I9[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
   k.ncon = 0;
@@ -996,6 +998,7 @@ JHD JNOINLINE void fast_arm_collide(const ChainOut& c, const FreeBody& fo, const
   }
   FAST_WSTAT(11);
   if (cand) FAST_WSTAT(12);
+  if (cand_out) { *cand_out = cand; return; }
   if (!cand) return;
   if (JACO_TIMING_SKIP & 4) { k.ncon = (int)(cand >> 63); return; }
   // ---- narrow phase, one routine at a time so that lanes working on different pairs stay converged
@@ -1182,23 +1185,38 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
       FAST_WSTAT(0);
       if (need) { FAST_WSTAT(1); if (bail & BAIL_LIMIT) FAST_WSTAT(8); if (bail & (BAIL_HAND | BAIL_FOREARM)) FAST_WSTAT(9); if (bail & (BAIL_OBJ | BAIL_DEST)) FAST_WSTAT(10); }
 #ifdef __CUDA_ARCH__
-      unsigned pending = __ballot_sync(0xffffffffu, needB);
-      const int mylane = threadIdx.x & 31;
-      while (pending) {
-        const int L = __ffs(pending) - 1; pending &= pending - 1;
+      // Block-wide task queue: every lane that needs stage B takes a slot; the block's warps then serve the slots one
+      // task per warp and round, so the block waits for ceil(tasks / warps) cooperative solves instead of for the
+      // warp that happens to own the most.  Owners publish into the workspace of the serving warp (all owners of a
+      // round at the same time) and read their results back from it.
+      __shared__ int q_n;
+      const int nwarps = blockDim.x >> 5, mywarp = threadIdx.x >> 5;
+      CoopWS* const wsbase = ws - mywarp;
+      if (threadIdx.x == 0) q_n = 0;
+      __syncthreads();
+      int slot = -1;
+      if (needB) slot = atomicAdd(&q_n, 1);
+      __syncthreads();
+      const int ntask = q_n;
+      for (int base = 0; base < ntask; base += nwarps) {
+        const bool mine = slot >= base && slot < base + nwarps;
         JPROF_T(t1);
-        if (mylane == L) { coop_publish(*ws, s, c, fo, fd, fsm, it == 49); coop_publish_contacts(*ws, ks, flags); }
-        __syncwarp();
+        if (mine) { CoopWS& wt = wsbase[slot - base]; coop_publish(wt, s, c, fo, fd, fsm, it == 49); coop_publish_contacts(wt, ks, flags); }
+        __syncthreads();
         JPROF_T(t2);
-        const int sv = coop_stageB(*ws);
-        __syncwarp();
-        JPROF_T(t3);
-        JPROF_ADD(8, 1); JPROF_ADD(9, t2 - t1); JPROF_ADD(2, t3 - t2); if (sv) JPROF_ADD(3, 1);
-        if (mylane == L) {
-          solved = sv;
-          if (sv) { for (int i = 0; i < JACO_NV; i++) { qacc_g[i] = ws->qacc[i]; fcon_g[i] = ws->fcon[i]; } if (it == 49) s.touch_now = touch_class(ws->touch); }
+        if (base + mywarp < ntask) {
+          const int sv = coop_stageB(*ws);
+          if ((threadIdx.x & 31) == 0) ws->solved = sv;
+          JPROF_T(t3);
+          JPROF_ADD(8, 1); JPROF_ADD(9, t2 - t1); JPROF_ADD(2, t3 - t2); if (sv) JPROF_ADD(3, 1);
         }
-        __syncwarp();
+        __syncthreads();
+        if (mine) {
+          const CoopWS& wt = wsbase[slot - base];
+          solved = wt.solved;
+          if (solved) { for (int i = 0; i < JACO_NV; i++) { qacc_g[i] = wt.qacc[i]; fcon_g[i] = wt.fcon[i]; } if (it == 49) s.touch_now = touch_class(wt.touch); }
+        }
+        if (base + nwarps < ntask) __syncthreads();   // the next round's owners overwrite the workspaces
       }
 #else
       if (needB) {

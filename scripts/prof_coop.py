@@ -1,21 +1,32 @@
-"""Cycle breakdown of the warp-cooperative path (needs a -DJACO_PROF build: JACO_B200_LIB=...)."""
+"""Cycle breakdown of the warp-cooperative path on an aged population (needs a -DJACO_PROF build:
+scripts/build_variant.sh prof -DJACO_PROF; JACO_B200_LIB=$PWD/mujoco_jaco_b200/libjaco_b200_prof.so).
+usage: python scripts/prof_coop.py [n_envs] [age_steps] [steps]"""
 import os, sys, ctypes as C
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
 from mujoco_jaco_b200.env import JacoVecEnv
-n = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 65536
+age = int(sys.argv[2]) if len(sys.argv) > 2 else 200
+steps = int(sys.argv[3]) if len(sys.argv) > 3 else 5
 env = JacoVecEnv(n, task="picking", seed=0, auto_reset=True)
 env.reset()
+env.L.jaco_debug_prof.argtypes = [C.c_void_p]
 g = torch.Generator(device="cuda").manual_seed(0)
-for k in range(6):
-    a = torch.rand(n, 7, device="cuda", generator=g) * 2 - 1
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(); env.step(a); e1.record(); torch.cuda.synchronize()
+acts = torch.rand(32, n, 7, device="cuda", generator=g) * 2 - 1
+def snap():
     out = np.zeros(16, np.uint64)
-    env.L.jaco_debug_prof.argtypes = [C.c_void_p]
-    rc = env.L.jaco_debug_prof(out.ctypes.data_as(C.c_void_p))
-    o = out.astype(np.float64)
-    print(k, "ms", round(e0.elapsed_time(e1), 2), "stageA calls", int(o[0]), "cyc/call %.0f" % (o[1] / max(o[0], 1)), "| stageB calls", int(o[8]), "publish %.0f" % (o[9] / max(o[8], 1)),
-          "stageB %.0f" % (o[2] / max(o[8], 1)), "collision %.0f" % (o[4] / max(o[8], 1)), "constraints %.0f" % (o[5] / max(o[8], 1)), "| solved", int(o[3]),
-          "solve cyc %.0f" % (o[6] / max(o[3], 1)), "iters %.2f" % (o[7] / max(o[3], 1)),
-          "| per solve: setup %.0f grad %.0f hess %.0f chol %.0f ls %.0f upd %.0f" % tuple(o[10 + k] / max(o[3], 1) for k in range(6)), flush=True)
+    env.L.jaco_debug_prof(out.ctypes.data_as(C.c_void_p))
+    return out.astype(np.float64)
+for k in range(age):
+    env.step(acts[k % 32])
+torch.cuda.synchronize()
+prev = snap()
+for k in range(steps):
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(); env.step(acts[(age + k) % 32]); e1.record(); torch.cuda.synchronize()
+    cur = snap(); o = cur - prev; prev = cur
+    nb, ns = max(o[8], 1), max(o[3], 1)
+    print(f"age {age + k}: {e0.elapsed_time(e1):.1f} ms | stage B calls {int(o[8])} ({100 * o[8] / (n * 50):.2f}% of env-substeps) "
+          f"publish {o[9] / nb:.0f} stageB {o[2] / nb:.0f} (collision {o[4] / nb:.0f} constraints {o[5] / nb:.0f}) cyc/call | "
+          f"solves {int(o[3])} {o[6] / ns:.0f} cyc, iters {o[7] / ns:.2f}: setup {o[10] / ns:.0f} grad {o[11] / ns:.0f} "
+          f"dir {o[12] / ns:.0f} ls {o[14] / ns:.0f} upd {o[15] / ns:.0f}", flush=True)
