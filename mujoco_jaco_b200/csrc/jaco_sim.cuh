@@ -32,7 +32,8 @@ static JacoModel g_jaco_model_host;
 
 #define JPI 3.14159265358979323846f
 #define JMINVAL 1e-15f
-#define JACO_SOLVER_MAXIT 8
+#define JACO_SOLVER_MAXIT 8            // Newton iterations per component (fast path / cooperative path)
+#define JACO_SOLVER_MAXIT_GENERAL 40   // general path: all coupled blocks are solved as one system, which needs more
 #define PK(i, j) ((i) * ((i) + 1) / 2 + (j))  // packed lower-triangular index, j <= i
 
 // ------------------------------------------------------------------------------------------- small math
@@ -935,6 +936,13 @@ JHD void solve_constraints(JacoSim& s) {
     for (int i = 0; i < JACO_NV; i++) { s.qacc[i] = s.asm_[i]; s.fcon[i] = 0; }
     return;
   }
+  // the direction components enter rows_cost as al * cp with al = 0 before the first line search: they must be
+  // finite (a stale Inf / NaN in this uninitialised working set would deactivate rows: found as a launched object)
+  for (int c = 0; c < s.ncon; c++)
+#pragma unroll
+    for (int k = 0; k < 6; k++) s.cp[c][k] = 0;
+#pragma unroll
+  for (int r = 0; r < 5; r++) s.lp[r] = 0;
   int mask = s.nlim ? 1 : 0;
   for (int c = 0; c < s.ncon; c++) { const JacoPair& P = m.pairs[s.cpair[c]]; mask |= body_block(m.geoms[P.g1].body) | body_block(m.geoms[P.g2].body); }
   // compact index of every dof inside the active system
@@ -958,17 +966,24 @@ JHD void solve_constraints(JacoSim& s) {
     for (int i = 0; i < JACO_NV; i++) a[i] = s.asm_[i];
   }
   float H[231], g[JACO_NV], p[JACO_NV], jf[JACO_NV];
-  for (int it = 0; it < JACO_SOLVER_MAXIT; it++) {
+  for (int it = 0; it < JACO_SOLVER_MAXIT_GENERAL; it++) {
     // gradient
     float d[JACO_NV];
 #pragma unroll
     for (int i = 0; i < JACO_NV; i++) d[i] = a[i] - s.asm_[i];
     mul_M(s, d, g);
     rows_force(s, jf);
-    float gn = 0, fn = 0;
+    // block-wise relative gradient test: each block (chain, object, dest) against its own force scale -- one global
+    // test lets the 1280 kg destination box hide an unconverged 17 g object (same rule as jaco_coop.cuh)
+    bool conv = true;
+    {
+      float gb[3] = {0, 0, 0}, fb[3] = {0, 0, 0};
 #pragma unroll
-    for (int i = 0; i < JACO_NV; i++) { fn += jf[i] * jf[i] + g[i] * g[i]; g[i] -= jf[i]; gn += g[i] * g[i]; }
-    if (gn <= 1e-12f * fn || gn < 1e-20f) break;
+      for (int i = 0; i < JACO_NV; i++) { const int b = i < 9 ? 0 : (i < 15 ? 1 : 2); fb[b] += jf[i] * jf[i] + g[i] * g[i]; g[i] -= jf[i]; gb[b] += g[i] * g[i]; }
+#pragma unroll
+      for (int b = 0; b < 3; b++) if ((mask >> b) & 1) { if (!(gb[b] <= 1e-12f * fb[b] || gb[b] < 1e-20f)) conv = false; }
+    }
+    if (conv) break;
     // Hessian over the active dofs
     for (int i = 0; i < n * (n + 1) / 2; i++) H[i] = 0;
     if (mask & 1) for (int i = 0; i < 9; i++) for (int j = 0; j <= i; j++) H[PK(off[0] + i, off[0] + j)] = s.Mc[PK(i, j)];
@@ -1648,6 +1663,9 @@ JHD void entry_reset(const JacoCfg& cfg, float* state, int N, int i, int env_id,
 JHD void entry_step(const JacoCfg& cfg, float* state, int N, int i, int env_id, const float* action_row, float* obs_row,
                     float* reward, unsigned char* done, unsigned char* succ, float* wb, float* term_obs_row, int auto_reset, float* local_stats) {
   JacoSim s;
+#ifdef JACO_POISON   /* CPU harness debugging: fill the working set with a byte pattern to expose reads of unset members */
+  memset((void*)&s, JACO_POISON, sizeof s);
+#endif
   load_env(state, N, i, s);
   refresh_lagged(s);
   float obs[JACO_NOBS], r, w; int d, sc;
