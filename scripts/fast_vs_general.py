@@ -9,8 +9,9 @@ def run(n, steps, tag):
     from mujoco_jaco_b200.env import JacoVecEnv
     env = JacoVecEnv(n, task="picking", seed=0, auto_reset=True)
     env.reset()
-    g = torch.Generator(device="cuda").manual_seed(0)
-    acts = [torch.rand(n, 7, device="cuda", generator=g) * 2 - 1 for _ in range(steps)]
+    rng = np.random.default_rng(0)   # numpy actions: a mismatching env can be replayed on the CPU against the oracle
+    acts_np = rng.uniform(-1, 1, (steps, n, 7)).astype(np.float32)
+    acts = [torch.from_numpy(acts_np[k]).cuda() for k in range(steps)]
     outs = []
     torch.cuda.synchronize()
     times = []
