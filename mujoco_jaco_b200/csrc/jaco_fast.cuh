@@ -1102,7 +1102,7 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
 #pragma unroll
   for (int i = 0; i < 7; i++) a[i] = fminf(fmaxf(action[i], -1.0f), 1.0f);
   if (cfg.task == JACO_TASK_REACHING) a[6] = 0;
-  take_action(s, a);
+  take_action(s, a, cfg.variant);
   if (cfg.task == JACO_TASK_REACHING) { s.grip = 0.6f; s.ramp0 = s.ramp1 = 0.6f; }
   euler_rxyz_to_quat(s.tq, s.target[3], s.target[4], s.target[5]);
   quat_normalize(s.tq);

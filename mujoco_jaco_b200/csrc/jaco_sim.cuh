@@ -1486,10 +1486,12 @@ JHD void substep(JacoSim& s, const float* u, int i, bool want_touch) {
   mj_euler(s);
 }
 template <class S>
-JHD void take_action(S& s, const float* a) {  // util:602-646
+JHD void take_action(S& s, const float* a, int variant = 0) {  // util:602-646
   s.action_in = 1;
   get_gripper_pose(s);
-  for (int i = 0; i < 3; i++) { s.target[i] = s.gripper_pose[i] + a[i] / 25; s.target[3 + i] = s.gripper_pose[3 + i] + a[3 + i] / 5; }
+  // base: a[:3]/25, a[3:6]/5 (util:621); _cis / _trans, single arm: a[:3]/100, a[3:6]/20 (env_mujoco_util_cis.py:776)
+  const float sp = variant == 0 ? 25.0f : 100.0f, sa = variant == 0 ? 5.0f : 20.0f;
+  for (int i = 0; i < 3; i++) { s.target[i] = s.gripper_pose[i] + a[i] / sp; s.target[3 + i] = s.gripper_pose[3 + i] + a[3 + i] / sa; }
   if (fabsf(s.target[5]) > JPI) s.target[5] += -(s.target[5] > 0 ? 1.0f : -1.0f) * 2 * JPI;
   float prev = s.grip, g = fminf(fmaxf(prev + a[6] / 10, 0.6f), 1.0f);
   s.grip = g; s.ramp0 = prev; s.ramp1 = g;
@@ -1573,7 +1575,7 @@ JHD void env_step(const JacoCfg& cfg, JacoSim& s, int env_id, const float* actio
   float a[7], u[6];
   for (int i = 0; i < 7; i++) a[i] = fminf(fmaxf(action[i], -1.0f), 1.0f);
   if (cfg.task == JACO_TASK_REACHING) a[6] = 0;
-  take_action(s, a);
+  take_action(s, a, cfg.variant);
   if (cfg.task == JACO_TASK_REACHING) { s.grip = 0.6f; s.ramp0 = s.ramp1 = 0.6f; }
   for (int i = 0; i < 50; i++) {
     osc_generate(s, s.qvel, u);

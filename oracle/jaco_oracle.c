@@ -1042,7 +1042,10 @@ static void set_obj(jo_env *e, const real *xyz, const real *quat) { /* mujoco.py
 static void take_action(jo_env *e, const real *a) { /* util:602-646 */
   e->action_in = 1; e->gripper_iter = 0;
   get_gripper_pose(e);
-  for (int i = 0; i < 3; i++) { e->target[i] = e->gripper_pose[i] + a[i] / 25; e->target[3 + i] = e->gripper_pose[3 + i] + a[3 + i] / 5; }
+  /* base: a[:3]/25, a[3:6]/5 (util:621); _cis / _trans single arm: a[:3]/100, a[3:6]/20
+   * (env_mujoco_util_cis.py:776, env_mujoco_util_trans.py:780) */
+  const real sp = e->variant == JO_VAR_BASE ? R_(25) : R_(100), sa = e->variant == JO_VAR_BASE ? R_(5) : R_(20);
+  for (int i = 0; i < 3; i++) { e->target[i] = e->gripper_pose[i] + a[i] / sp; e->target[3 + i] = e->gripper_pose[3 + i] + a[3 + i] / sa; }
   if (rabs(e->target[5]) > PI_) e->target[5] += -(e->target[5] > 0 ? R_(1) : R_(-1)) * 2 * PI_;
   real prev = e->gripper_angle, g = prev + a[6] / 10;
   if (g < R_(0.6)) g = R_(0.6); if (g > 1) g = 1;

@@ -49,7 +49,7 @@ extern "C" void hh_step_trace(int task, int variant, unsigned long long seed, in
   JacoSim s; load_env(state, N, i, s); refresh_lagged(s);
   float a[7], u[6];
   for (int k = 0; k < 7; k++) a[k] = fminf(fmaxf(action[k], -1.0f), 1.0f);
-  take_action(s, a);
+  take_action(s, a, c.variant);
   for (int k = 0; k < 50; k++) {
     osc_generate(s, s.qvel, u);
     substep(s, u, k, k == 49);

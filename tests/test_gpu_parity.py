@@ -149,3 +149,28 @@ def test_single_env_shim_runs_1000_random_steps(tmp_path):
             ndone += 1
             obs = env.reset()
     env.close()
+
+
+@pytest.mark.parametrize("task,variant", [("placing", "base"), ("pickAndplace", "cis"), ("picking", "trans"), ("placing", "cis")])
+def test_config4_tasks_and_variants_one_step(task, variant):
+    """BASELINE config 4: placing / pickAndplace and the _cis / _trans variants (base-relative observations,
+    a/100 - a/20 action scale, 3-tuple terminal logic): reset (placing = 150 in-hand settle substeps) and one env
+    step against the oracle.  Placing starts with the object held between the fingers (contact-rich, chaotic), so
+    the bar is on the fraction of envs that agree."""
+    from mujoco_jaco_b200.env import JacoVecEnv
+    n = 64
+    env = JacoVecEnv(n, task=task, variant=variant, seed=13, auto_reset=False)
+    obs = env.reset().cpu().numpy()
+    ora = _oracles(task, 13, n, variant=variant)
+    oobs = np.stack([o.reset() for o in ora])
+    bad_reset = np.abs(obs - oobs).max(1) > (2e-3 if task == "placing" else 5e-6)
+    assert bad_reset.mean() <= (0.1 if task == "placing" else 0.0), f"reset: {bad_reset.sum()} of {n} envs off"
+    a = np.random.default_rng(17).uniform(-1, 1, (n, 7)).astype(np.float32)
+    o1, r1, d1, s1 = [t.cpu().numpy() for t in env.step(torch.from_numpy(a).cuda())]
+    ref = [o.step(a[i].astype(np.float64)) for i, o in enumerate(ora)]
+    ro = np.stack([x[0] for x in ref]); rr = np.array([x[1] for x in ref]); rd = np.array([x[2] for x in ref])
+    good = ~bad_reset
+    tol = 5e-3 if task == "placing" else 1e-3
+    off = (np.abs(o1 - ro).max(1) > tol) | (np.abs(r1 - rr) > 1e-3)
+    assert off[good].mean() <= (0.15 if task == "placing" else 0.03), f"step: {off[good].sum()} of {good.sum()} envs off"
+    assert (d1.astype(bool) != rd)[good].mean() <= 0.03

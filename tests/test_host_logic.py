@@ -146,3 +146,30 @@ def test_general_and_hybrid_paths_agree_with_oracle_when_arm_rests_on_dest(eid):
     og = hg.step(act[None]); of = hf.step_fast(act[None], allow_fallback=2); oo = o.step(act.astype(np.float64))
     assert abs(og[0][0, 10] - oo[0][10]) < 1e-4 and abs(of[0][0, 10] - oo[0][10]) < 1e-4
     assert abs(og[1][0] - oo[1]) < 1e-4 and abs(of[1][0] - oo[1]) < 1e-4
+
+
+@pytest.mark.parametrize("variant", ["cis", "trans"])
+def test_variant_action_scale_cis_trans(variant):
+    """_cis / _trans single-arm action scale a[:3]/100, a[3:6]/20 (env_mujoco_util_cis.py:776,
+    env_mujoco_util_trans.py:780) against the oracle, general and hybrid path, and against the base scale."""
+    from hostsim import HostSim
+    n = 4
+    act = np.random.default_rng(7).uniform(-1, 1, (n, 7)).astype(np.float32)
+    hg = HostSim(n, task="picking", variant=variant, seed=3); hg.reset()
+    hf = HostSim(n, task="picking", variant=variant, seed=3); hf.reset()
+    ora = _oracles("picking", 3, n, variant=variant)
+    for o in ora:
+        o.reset()
+    q0 = hg.get_state()[0].copy()
+    og = hg.step(act); of = hf.step_fast(act, allow_fallback=2)
+    oo = [o.step(act[i].astype(np.float64)) for i, o in enumerate(ora)]
+    oobs = np.stack([x[0] for x in oo])
+    assert np.abs(og[0] - oobs).max() < 2e-4 and np.abs(of[0] - oobs).max() < 2e-4
+    # the OSC target moved by a/100 (not a/25): aux rows 0..2 hold the target position
+    aux = hg.get_state()[2]
+    hb = HostSim(n, task="picking", variant="base", seed=3); hb.reset(); hb.step(act)
+    auxb = hb.get_state()[2]
+    hs0 = HostSim(n, task="picking", variant=variant, seed=3); hs0.reset(); hs0.step(np.zeros((n, 7), np.float32))
+    aux0 = hs0.get_state()[2]
+    assert np.allclose(aux[:, 0:3] - aux0[:, 0:3], act[:, 0:3] / 100, atol=2e-6)
+    assert not np.allclose(aux[:, 0:3], auxb[:, 0:3], atol=1e-4)
