@@ -20,6 +20,7 @@ import time
 
 REPO = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, REPO)
+_OUT = sys.stdout
 
 # algorithmic bytes per env-step of the step kernel (DESIGN.md "roofline"): SoA state rows read + written
 # (23 qpos + 21 qvel + 72 aux floats each way) + action 28 B + obs 104 B + reward 4 + wb 4 + done 1 + succ 1
@@ -116,13 +117,13 @@ def run_reference(args):
             vals.append(cb["value"])
     v = sum(vals) / len(vals)
     cb["value"] = v
-    print(json.dumps({
+    print(file=_OUT, flush=True, *[json.dumps({
         "impl": "reference", "metric": "jaco_picking_env_steps_per_sec", "value": v, "unit": "env-steps/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * per_step_s,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": "picking roll-out, 1 env per host process (CPU restatement of JacoMujocoEnv.step)"},
         "cpu_baseline": cb, "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })])
 
 
 def main():
@@ -139,6 +140,11 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    # stdout carries exactly one JSON line: libraries that log to fd 1 (NCCL's version banner) are sent to stderr
+    global _OUT
+    sys.stdout.flush()
+    _OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         return run_reference(args)
 
@@ -253,7 +259,7 @@ def main():
         }
         if not args.no_cpu_baseline and world == 1:
             out["cpu_baseline"] = cpu_baseline(args.cpu_seconds)
-        print(json.dumps(out))
+        print(json.dumps(out), file=_OUT, flush=True)
     if world > 1:
         dist.destroy_process_group()
 
