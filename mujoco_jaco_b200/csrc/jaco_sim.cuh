@@ -1234,20 +1234,30 @@ JHD void sym_pinv6(const float* X, float rcond, float* out) {  // numpy.linalg.p
     for (int i = 0; i < 6; i++) { dg += A[i][i] * A[i][i]; for (int j = i + 1; j < 6; j++) off += A[i][j] * A[i][j]; }
     if (off <= 1e-14f * dg) break;
     for (int p = 0; p < 6; p++) for (int q = p + 1; q < 6; q++) {
-      if (fabsf(A[p][q]) < 1e-30f) continue;
-      float th = (A[q][q] - A[p][p]) / (2 * A[p][q]);
+      const float apq = A[p][q];
+      if (fabsf(apq) < 1e-30f) continue;
+      float th = (A[q][q] - A[p][p]) / (2 * apq);
       float t = (th >= 0 ? 1.0f : -1.0f) / (fabsf(th) + sqrtf(th * th + 1)), c = 1.0f / sqrtf(t * t + 1), sn = t * c;
-      for (int k = 0; k < 6; k++) { float akp = A[k][p], akq = A[k][q]; A[k][p] = c * akp - sn * akq; A[k][q] = sn * akp + c * akq; }
-      for (int k = 0; k < 6; k++) { float apk = A[p][k], aqk = A[q][k]; A[p][k] = c * apk - sn * aqk; A[q][k] = sn * apk + c * aqk; }
+      // symmetric two-sided rotation: only rows / columns p, q change, the (p, q) entry is annihilated exactly
+      // (half the work of rotating columns and rows separately; this branch is 16 % of the aged step's instructions)
+      for (int k = 0; k < 6; k++) {
+        if (k == p || k == q) continue;
+        const float akp = A[k][p], akq = A[k][q];
+        const float np_ = c * akp - sn * akq, nq_ = sn * akp + c * akq;
+        A[k][p] = np_; A[p][k] = np_; A[k][q] = nq_; A[q][k] = nq_;
+      }
+      A[p][p] -= t * apq; A[q][q] += t * apq; A[p][q] = 0; A[q][p] = 0;
       for (int k = 0; k < 6; k++) { float vkp = V[k][p], vkq = V[k][q]; V[k][p] = c * vkp - sn * vkq; V[k][q] = sn * vkp + c * vkq; }
     }
   }
   float lmax = 0;
   for (int i = 0; i < 6; i++) lmax = fmaxf(lmax, fabsf(A[i][i]));
-  for (int i = 0; i < 6; i++) for (int j = 0; j < 6; j++) {
+  float inv[6];   // 1 / lambda_k of the kept eigenvalues, 0 for the truncated ones (6 divisions instead of 216)
+  for (int k = 0; k < 6; k++) inv[k] = fabsf(A[k][k]) > rcond * lmax ? 1.0f / A[k][k] : 0.0f;
+  for (int i = 0; i < 6; i++) for (int j = 0; j <= i; j++) {
     float sm = 0;
-    for (int k = 0; k < 6; k++) if (fabsf(A[k][k]) > rcond * lmax) sm += V[i][k] * V[j][k] / A[k][k];
-    out[6 * i + j] = sm;
+    for (int k = 0; k < 6; k++) sm += V[i][k] * inv[k] * V[j][k];
+    out[6 * i + j] = sm; out[6 * j + i] = sm;
   }
 }
 // abr_control OSC.generate with kp=50 ko=180 kv=20 vmax=[0.4,1.0472] (env_mujoco_util.py:59-63), reading the
