@@ -7,10 +7,11 @@ import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 REPO = os.path.dirname(HERE)
-SO_PATH = os.environ.get("JACO_B200_LIB") or os.path.join(HERE, "libjaco_b200.so")  # override: diagnostic builds only
+SO_PATH = os.path.join(HERE, "libjaco_b200.so")
 CSRC = os.path.join(HERE, "csrc")
-UNITS = ["jaco_kernels.cu", "jaco_kernel_fast.cu", "jaco_kernel_coop.cu"]   # compiled in parallel, linked into one .so
-HEADERS = [os.path.join(CSRC, f) for f in ("jaco_sim.cuh", "jaco_fast.cuh", "jaco_coop.cuh", "jaco_launch.h", "jaco_model.h")] + [
+UNITS = ["jaco_kernels.cu", "jaco_kernel_pipe.cu"]            # compiled in parallel, linked into one .so
+DIAG_UNITS = ["jaco_kernel_fast.cu", "jaco_kernel_coop.cu"]   # round-1 fused kernels: only in -DJACO_DIAG builds (scripts/build_variant.sh)
+HEADERS = [os.path.join(CSRC, f) for f in ("jaco_sim.cuh", "jaco_fast.cuh", "jaco_coop.cuh", "jaco_pipe.cuh", "jaco_launch.h", "jaco_model.h")] + [
     os.path.join(REPO, "include", "jaco_b200.h"), os.path.join(REPO, "include", "jaco_model_layout.h")]
 SOURCES = [os.path.join(CSRC, u) for u in UNITS] + HEADERS
 # -prec-div=false -prec-sqrt=false -ftz=true: 2-ulp division / square root and flushed denormals.  IEEE division and
@@ -44,7 +45,7 @@ def build(force=False, verbose=False, defines=(), out=None):
     os.makedirs(objdir, exist_ok=True)
     hdr_t = max(os.path.getmtime(h) for h in HEADERS)
     procs, objs = [], []
-    for u in UNITS:
+    for u in UNITS + (DIAG_UNITS if any(d.startswith("JACO_DIAG") for d in defines) else []):
         src, obj = os.path.join(CSRC, u), os.path.join(objdir, u[:-3] + ".o")
         objs.append(obj)
         if not force and os.path.exists(obj) and os.path.getmtime(obj) > max(hdr_t, os.path.getmtime(src)):
@@ -61,15 +62,17 @@ def build(force=False, verbose=False, defines=(), out=None):
 _lib = None
 
 
-def load():
+def load(path=None):
+    """Load the library (once per process).  `path`: a diagnostic build made with build(defines=..., out=...)."""
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(SO_PATH):
+    path = path or SO_PATH
+    if not os.path.exists(path):
         raise RuntimeError(
-            f"{SO_PATH} is missing: the CUDA extension has not been built (run `python -c 'import __graft_entry__ as g; "
+            f"{path} is missing: the CUDA extension has not been built (run `python -c 'import __graft_entry__ as g; "
             "g.build()'`).  mujoco_jaco_b200 has no CPU fallback.")
-    L = C.CDLL(SO_PATH)
+    L = C.CDLL(path)
     vp, f, u8 = C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_uint8)
     L.jaco_create.argtypes = [vp, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_int, C.POINTER(vp)]
     L.jaco_destroy.argtypes = [vp]

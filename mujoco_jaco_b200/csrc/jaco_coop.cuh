@@ -58,9 +58,10 @@ struct CoopSink {  // contacts of one geom pair (<= 8: box-box clipping cap)
   float cpos[8][3], cn[8][3], cdist[8];
 };
 
-struct CoopWS {
-  static JHD const JacoModel& model() { return MDLG; }
-  // ---- published by the owner thread (mjData of this substep's forward pass)
+// What the owner thread publishes: the mj_forward quantities of this substep the cooperative path consumes.  Kept as the
+// leading base sub-object of CoopWS so that the pipeline (jaco_pipe.cuh) can stage it through a global-memory record
+// and copy it word by word into a warp's shared-memory workspace.
+struct CoopPub {
   float bx[JACO_NBODY][3], bR[JACO_NBODY][9], ax[9][3], bw[JACO_NBODY][3], bv[JACO_NBODY][3];
   float qpos9[9], qvel[JACO_NV], Mc[45], Mf[2][21], asm_[JACO_NV], warm[JACO_NV];
   int want_touch, flags;      // flags: COOP_SIMPLE_OBJ | COOP_FORCE_B
@@ -68,6 +69,9 @@ struct CoopWS {
   // ---- arm contacts the owner thread found with its own narrow phase (fast_arm_collide), in pair order
   int pre_ncon, pre_pair[24];
   float pre_pos[24][3], pre_n[24][3], pre_dist[24];
+};
+struct CoopWS : CoopPub {
+  static JHD const JacoModel& model() { return MDLG; }
   // ---- contacts and rows
   int ncon, nlim, arm_rows;
   int cpair[JACO_MAXCON], cmask[JACO_MAXCON], ccond[JACO_MAXCON], croff[JACO_MAXCON];

@@ -286,9 +286,22 @@ JHD int chain_solve(const ChainOut& c, float hdt, const float* r, float* x) {
 }
 
 // abr_control OSC.generate on the quantities of one forward, without explicit inverses:
-// A = L L^T, Y = L^-1 J^T, Mx_inv = Y^T Y, Mx u_task by a second Cholesky.  Returns 0 when the reference would
-// take the pinv branch (|det Mx_inv| < 1e-3) or a pivot fails -- the caller bails to the general path.
-JHD int fast_osc(const ChainOut& c, const float* tq, const float* target, const float* dq, float* u, bool allow_pinv = false) {
+// A = L L^T, Y = L^-1 J^T, Mx_inv = Y^T Y, Mx u_task by a second Cholesky.
+// When the reference takes the pinv branch (|det Mx_inv| < 1e-3, numpy.linalg.pinv(Mx_inv, rcond = 1e-4)) or a pivot
+// fails, `mode` decides: OSC_BAIL returns 0 (caller leaves the fast path), OSC_INLINE runs the Jacobi
+// eigen-decomposition here, OSC_DEFER fills `od` with what osc_finish_pinv needs and returns 2 (the pipeline hands
+// these rare, slow cases to its dirty-env stream so the main kernel never executes the eigen-solver).
+enum { OSC_BAIL = 0, OSC_INLINE = 1, OSC_DEFER = 2 };
+struct OscDefer { float X[21], ut[6], u0[6], J[6][6]; };   // Mx_inv (packed lower), scaled task error, -kv M dq + bias, EE Jacobian
+JHD void osc_finish_pinv(const OscDefer& od, float* u) {
+  float Xf[36], Mx[36], f[6];
+  for (int i = 0; i < 6; i++) for (int j = 0; j < 6; j++) Xf[6 * i + j] = od.X[i >= j ? PK(i, j) : PK(j, i)];
+  FAST_WSTAT(15);
+  sym_pinv6(Xf, 1e-4f, Mx);
+  for (int i = 0; i < 6; i++) { float sm = 0; for (int j = 0; j < 6; j++) sm += Mx[6 * i + j] * od.ut[j]; f[i] = sm; }
+  for (int i = 0; i < 6; i++) { float tt = 0; for (int j = 0; j < 6; j++) tt += od.J[j][i] * f[j]; u[i] = od.u0[i] - tt; }
+}
+JHD int fast_osc(const ChainOut& c, const float* tq, const float* target, const float* dq, float* u, int mode = OSC_BAIL, OscDefer* od = nullptr) {
   const float kp = 50, ko = 180, kv = 20, vmax0 = 0.4f, vmax1 = 1.0472f;
   float L[21], Y[6][6], X[21];
 #pragma unroll
@@ -305,6 +318,7 @@ JHD int fast_osc(const ChainOut& c, const float* tq, const float* target, const 
       Y[r][i] = sm / L[PK(r, r)];
     }
   }
+  float X0[21];
 #pragma unroll
   for (int i = 0; i < 6; i++)
 #pragma unroll
@@ -312,14 +326,14 @@ JHD int fast_osc(const ChainOut& c, const float* tq, const float* target, const 
       float sm = 0;
 #pragma unroll
       for (int k = 0; k < 6; k++) sm += Y[k][i] * Y[k][j];
-      X[PK(i, j)] = sm;
+      X[PK(i, j)] = sm; X0[PK(i, j)] = sm;
     }
   ok &= chol_packed<6>(X);
   float det = 1;
 #pragma unroll
   for (int i = 0; i < 6; i++) det *= X[PK(i, i)] * X[PK(i, i)];
   const bool singular = !ok || !(fabsf(det) >= 1e-3f);
-  if (singular && !allow_pinv) return 0;
+  if (singular && mode == OSC_BAIL) return 0;
   float ut[6];
 #pragma unroll
   for (int i = 0; i < 3; i++) ut[i] = c.eepos[i] - target[i];
@@ -332,20 +346,29 @@ JHD int fast_osc(const ChainOut& c, const float* tq, const float* target, const 
   if (na > sat_abg) { float r = sat_abg / na; sc[3] *= r; sc[4] *= r; sc[5] *= r; }
 #pragma unroll
   for (int i = 0; i < 6; i++) ut[i] = kv * sc[i] * ((i < 3 ? kp : ko) / kv) * ut[i];
-  if (!singular) chol_solve_packed<6>(X, ut);  // ut <- Mx u_task
-  else {  // numpy.linalg.pinv(Mx_inv, rcond = 1e-4) branch of the reference controller (rare)
-    float Xf[36], Mx[36], f[6];
-    for (int i = 0; i < 6; i++) for (int j = 0; j < 6; j++) { float sm = 0; for (int k = 0; k < 6; k++) sm += Y[k][i] * Y[k][j]; Xf[6 * i + j] = sm; }
-    sym_pinv6(Xf, 1e-4f, Mx);
-    for (int i = 0; i < 6; i++) { float sm = 0; for (int j = 0; j < 6; j++) sm += Mx[6 * i + j] * ut[j]; f[i] = sm; }
-    for (int i = 0; i < 6; i++) ut[i] = f[i];
-  }
+  float u0[6];
 #pragma unroll
   for (int i = 0; i < 6; i++) {
-    float sm = 0, tt = 0;
+    float sm = 0;
 #pragma unroll
-    for (int j = 0; j < 6; j++) { sm += c.A[i >= j ? PK(i, j) : PK(j, i)] * dq[j]; tt += c.J[j][i] * ut[j]; }
-    u[i] = -kv * sm - tt + c.bias[i];
+    for (int j = 0; j < 6; j++) sm += c.A[i >= j ? PK(i, j) : PK(j, i)] * dq[j];
+    u0[i] = -kv * sm + c.bias[i];
+  }
+  if (singular) {  // numpy.linalg.pinv(Mx_inv, rcond = 1e-4) branch of the reference controller (rare)
+    OscDefer loc; OscDefer& d = (mode == OSC_DEFER) ? *od : loc;
+    for (int i = 0; i < 21; i++) d.X[i] = X0[i];
+    for (int i = 0; i < 6; i++) { d.ut[i] = ut[i]; d.u0[i] = u0[i]; for (int j = 0; j < 6; j++) d.J[i][j] = c.J[i][j]; }
+    if (mode == OSC_DEFER) return 2;
+    osc_finish_pinv(d, u);
+    return 1;
+  }
+  chol_solve_packed<6>(X, ut);  // ut <- Mx u_task
+#pragma unroll
+  for (int i = 0; i < 6; i++) {
+    float tt = 0;
+#pragma unroll
+    for (int j = 0; j < 6; j++) tt += c.J[j][i] * ut[j];
+    u[i] = u0[i] - tt;
   }
   return 1;
 }
@@ -806,7 +829,7 @@ static inline bool fast_model_ok(const JacoModel& m) {
 }
 
 // Owner thread -> warp workspace, stage A: poses of the geom-carrying bodies only (cheap; no kinematics redone)
-JHD void coop_publish_poses(CoopWS& w, const ChainOut& c, const FreeBody& fo, const FreeBody& fd, int flags) {
+JHD void coop_publish_poses(CoopPub& w, const ChainOut& c, const FreeBody& fo, const FreeBody& fd, int flags) {
   v3set(w.bx[0], 0, 0, 0);
   { const float I[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}; for (int i = 0; i < 9; i++) w.bR[0][i] = I[i]; }
   for (int b = 3; b <= 9; b++) { v3copy(w.bx[b], c.bp[b - 3]); for (int i = 0; i < 9; i++) w.bR[b][i] = c.bRm[b - 3][i]; }
@@ -815,7 +838,7 @@ JHD void coop_publish_poses(CoopWS& w, const ChainOut& c, const FreeBody& fo, co
   w.flags = flags;
 }
 // Owner thread -> warp workspace: the mj_forward quantities of this substep the cooperative path consumes.
-JHD void coop_publish(CoopWS& w, const FastSim& s, const ChainOut& c, const FreeBody& fo, const FreeBody& fd, const float* fsm9, int want_touch) {
+JHD void coop_publish(CoopPub& w, const FastSim& s, const ChainOut& c, const FreeBody& fo, const FreeBody& fd, const float* fsm9, int want_touch) {
   const JacoModel& m = MDL;
   v3set(w.bx[0], 0, 0, 0); v3set(w.bw[0], 0, 0, 0); v3set(w.bv[0], 0, 0, 0);
   { const float I[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}; for (int i = 0; i < 9; i++) w.bR[0][i] = I[i]; }
@@ -1038,7 +1061,7 @@ JHD JNOINLINE void fast_arm_collide(const ChainOut& c, const FreeBody& fo, const
 
 // Owner thread -> warp workspace: its pre-collided arm contacts; stage B then runs its narrow phase on the scene
 // pairs 0..3 only.
-JHD void coop_publish_contacts(CoopWS& w, const LocalSink& k, int flags) {
+JHD void coop_publish_contacts(CoopPub& w, const LocalSink& k, int flags) {
   w.flags = flags; w.cand[0] = 0xFu; w.cand[1] = 0u;
   w.pre_ncon = k.ncon;
   for (int j = 0; j < k.ncon; j++) { v3copy(w.pre_pos[j], k.cpos[j]); v3copy(w.pre_n[j], k.cn[j]); w.pre_dist[j] = k.cdist[j]; w.pre_pair[j] = k.cpair[j]; }
@@ -1077,18 +1100,28 @@ JHD void free_integrate(const FreeBody& fb, const float* a6, const float* fcon6,
   }
 }
 
-// One env step on the fast path.  Returns FAST_OK with all outputs written into s / obs / ..., or FAST_BAIL
-// (reason bits in *why) with s in an unspecified state -- the caller must not store it.
-// COOP = true: nothing bails for contact reasons; environments that need the general contact handling get it from
-// the warp-cooperative path (jaco_coop.cuh) through the per-warp workspace ws, substep by substep.  All lanes of a
-// warp must then call this function together (lanes without an environment pass active = false).
-template <bool COOP>
-JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* action, float* obs, float* reward, int* done, int* succ, float* wb, int* why,
-                      CoopWS* ws = nullptr, bool active = true) {
+// ------------------------------------------------------------------------------------------- step pieces
+// The env step is cut into pieces that the legacy one-kernel path (fast_env_step below: CPU harness, diagnostics) and the
+// per-substep pipeline (jaco_pipe.cuh: the production kernels) share:
+//   step_begin    lagged controller data, _take_action, first OSC torque
+//   sub_forward   mj_forward of the fast regime at the current state: limits, free boxes, scene contacts, chain pass
+//   sub_finish    mj_Euler for the three blocks (with the cooperative path's qacc / fcon where it solved a block),
+//                 bookkeeping of the last substep, OSC torque for the next substep
+//   step_end      observation, reward, terminal logic (env_mujoco.py:116-150)
+struct SubFwd {
+  ChainOut c; FreeBody fo, fd; Con4 co, cd; float fsm[9]; int bail;
+};
+JHD void scene_static(SceneBoxes& sb) {
   const JacoModel& m = MDL;
-  const float h = m.dt;
+  const JacoGeom& G = m.geoms[FG_HOLDER];
+  v3copy(sb.hp, G.pos); v3copy(sb.hh, G.size);
+#pragma unroll
+  for (int i = 0; i < 9; i++) sb.hR[i] = G.R[i];
+  v3copy(sb.oh, m.geoms[FG_OBJ].size); v3copy(sb.dh, m.geoms[FG_DEST].size);
+}
+// returns 0 when the first OSC torque needs the pinv branch and osc_mode == OSC_BAIL; 2 when deferred into *od
+JHD int step_begin(const JacoCfg& cfg, FastSim& s, const float* action, int osc_mode, OscDefer* od) {
   ChainOut c;
-  *why = 0;
   {  // rebuild the controller-visible mjData at the lagged chain state
     const float O0[3] = {0, 0, 0.5f};
     fast_chain<false>(s.lagq, s.lagv, O0, nullptr, c);
@@ -1103,75 +1136,138 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
   for (int i = 0; i < 7; i++) a[i] = fminf(fmaxf(action[i], -1.0f), 1.0f);
   if (cfg.task == JACO_TASK_REACHING) a[6] = 0;
   take_action(s, a, cfg.variant);
-  if (cfg.task == JACO_TASK_REACHING) { s.grip = 0.6f; s.ramp0 = s.ramp1 = 0.6f; }
+  if (cfg.task == JACO_TASK_REACHING) { s.grip = 0.6f; s.ramp0 = s.ramp1 = 0.0f; }   // util:37,76-79,625-626
   euler_rxyz_to_quat(s.tq, s.target[3], s.target[4], s.target[5]);
   quat_normalize(s.tq);
   s.touch_now = 0;
-  int dead = 0;  // COOP: bail reason latched, the thread keeps pace with its warp until the step ends
-  if (!fast_osc(c, s.tq, s.target, s.qvel, s.u, COOP)) { *why = BAIL_OSC; if (!COOP) return FAST_BAIL; dead |= BAIL_OSC; }
-  // static holder box
-  SceneBoxes sb;
-  { const JacoGeom& G = m.geoms[FG_HOLDER];
-    v3copy(sb.hp, G.pos); v3copy(sb.hh, G.size);
-#pragma unroll
-    for (int i = 0; i < 9; i++) sb.hR[i] = G.R[i]; }
-  v3copy(sb.oh, m.geoms[FG_OBJ].size); v3copy(sb.dh, m.geoms[FG_DEST].size);
+  return fast_osc(c, s.tq, s.target, s.qvel, s.u, osc_mode, od);
+}
+template <bool COOP>
+JHD void sub_forward(FastSim& s, SceneBoxes& sb, int it, SubFwd& f) {
+  const JacoModel& m = MDL;
   const JacoGeom& GF = m.geoms[FG_FLOOR];
+  // ---- joint limits (mj_instantiateLimit): any active limit row leaves the fast regime
+  int bail = 0;
+#pragma unroll
+  for (int k = 0; k < 9; k++)
+    if (m.ch_limited[k] && (s.qpos[k] - m.ch_range[k][0] < 0 || m.ch_range[k][1] - s.qpos[k] < 0)) bail |= BAIL_LIMIT;
+  // ---- free boxes at the current state
+  FreeBody& fo = f.fo; FreeBody& fd = f.fd;
+  free_body_setup(10, FG_OBJ, s.qpos + 9, s.qvel + 9, fo);
+  JSYNC3();
+  free_body_setup(11, FG_DEST, s.qpos + 16, s.qvel + 15, fd);
+  JSYNC3();
+  v3copy(s.objp, fo.x);
+  v3copy(sb.op, fo.gp); v3copy(sb.dp, fd.gp);
+#pragma unroll
+  for (int i = 0; i < 9; i++) { sb.oR[i] = fo.gR[i]; sb.dR[i] = fd.gR[i]; }
+  // ---- scene contacts
+  {  // object: holder (box-box face) or floor (plane-box); both at once or anything else -> general path
+    Con4 cf; con4_clear(cf);
+    float dz[3]; v3sub(dz, fo.gp, GF.pos);
+    float pn[3] = {GF.R[2], GF.R[5], GF.R[8]};
+    if (v3dot(dz, pn) - m.geoms[FG_OBJ].rbound <= m.pairs[FP_FLOOR_OBJ].margin)
+      fast_plane_box(FP_FLOOR_OBJ, GF.pos, GF.R, fo.gp, fo.gR, sb.oh, m.pairs[FP_FLOOR_OBJ].margin, cf);
+    int rc = fast_box_box_face(FP_HOLDER_OBJ, sb.hp, sb.hR, sb.hh, fo.gp, fo.gR, sb.oh, m.pairs[FP_HOLDER_OBJ].margin, f.co);
+    if (rc < 0) bail |= BAIL_OBJ;
+    int nf = con4_count(cf), nh = rc > 0 ? con4_count(f.co) : 0;
+    if (nf > 0 && nh > 0) bail |= BAIL_OBJ;
+    if (nh == 0) f.co = cf;
+    float dd[3]; v3sub(dd, fd.gp, fo.gp);
+    if (!(v3norm(dd) > m.geoms[FG_DEST].rbound + m.geoms[FG_OBJ].rbound + m.pairs[FP_DEST_OBJ].margin)) bail |= BAIL_OBJ;
+  }
+  JSYNC3();
+  fast_plane_box(FP_FLOOR_DEST, GF.pos, GF.R, fd.gp, fd.gR, sb.dh, m.pairs[FP_FLOOR_DEST].margin, f.cd);
+  JSYNC2();
+  // ---- chain dynamics at (q, v), reference point = EE position of the previous forward
+  float O[3]; v3copy(O, s.eepos);
+  fast_chain<true>(s.qpos, s.qvel, O, &sb, f.c);
+  bail |= f.c.near;
+  f.bail = bail;
+  JSYNC2();
+  // ---- actuation + smooth forces of the chain (fwd_actuation, mj_passive)
+  const float gcmd = ramp_value(s, it);
+#pragma unroll
+  for (int i = 0; i < 6; i++) f.fsm[i] = fminf(fmaxf(s.u[i], m.motor_fr[i][0]), m.motor_fr[i][1]) - f.c.bias[i] - m.ch_damping[i] * s.qvel[i];
+#pragma unroll
+  for (int i = 0; i < 3; i++) {
+    const float* A = m.finger_act[i];
+    float cc = fminf(fmaxf(gcmd, A[1]), A[2]);
+    float fr = A[0] * cc - A[0] * s.qpos[6 + i];
+    f.fsm[6 + i] = fminf(fmaxf(fr, A[3]), A[4]) - f.c.bias[6 + i] - m.ch_damping[6 + i] * s.qvel[6 + i];
+  }
+}
+// solved: bit mask of the blocks (1 chain, 2 object, 4 dest) whose qacc_g / fcon_g come from the cooperative path.
+// Returns BAIL_* bits (0 = fine); osc_ret: result of the OSC for the next substep (1 done, 0 bail, 2 deferred into *od).
+template <bool COOP>
+JHD int sub_finish(FastSim& s, SubFwd& f, int it, int solved, const float* qacc_g, const float* fcon_g, int osc_mode, OscDefer* od, int* osc_ret) {
+  const float h = MDL.dt;
+  int dead = 0;
+  float acc[9];
+  *osc_ret = 1;
+  if (it == 49) {  // what the next env step needs from this forward
+    if (solved & 1) { for (int i = 0; i < 9; i++) s.warm[i] = qacc_g[i]; }
+    else { chain_solve(f.c, 0.0f, f.fsm, acc); for (int i = 0; i < 9; i++) s.warm[i] = acc[i]; }
+#pragma unroll
+    for (int i = 0; i < 9; i++) { s.lagq[i] = s.qpos[i]; s.lagv[i] = s.qvel[i]; }
+  }
+  // ---- mj_Euler, chain (implicit joint damping)
+  if (solved & 1) { for (int i = 0; i < 9; i++) f.fsm[i] += fcon_g[i]; }
+  if (!chain_solve(f.c, h, f.fsm, acc)) dead |= BAIL_NAN;
+  JSYNC3();
+#pragma unroll
+  for (int i = 0; i < 9; i++) { s.qvel[i] += h * acc[i]; s.qpos[i] += h * s.qvel[i]; }
+  // ---- free boxes: contact solve + Euler
+  if (solved & 2) free_integrate(f.fo, qacc_g + 9, fcon_g + 9, s.qpos + 9, s.qvel + 9, s.warm + 9);
+  else fast_free_step(f.fo, f.co, s.qpos + 9, s.qvel + 9, s.warm + 9);
+  JSYNC3();
+  if (solved & 4) free_integrate(f.fd, qacc_g + 15, fcon_g + 15, s.qpos + 16, s.qvel + 15, s.warm + 15);
+  else fast_free_step(f.fd, f.cd, s.qpos + 16, s.qvel + 15, s.warm + 15);
+  JSYNC2();
+  // ---- controller output for the next substep from this forward's mjData and the fresh joint velocity
+  v3copy(s.eepos, f.c.eepos);
+#pragma unroll
+  for (int i = 0; i < 4; i++) s.eeq[i] = f.c.eeq[i];
+  if (it < 49) { *osc_ret = fast_osc(f.c, s.tq, s.target, s.qvel, s.u, osc_mode, od); if (*osc_ret == 0) dead |= BAIL_OSC; }
+  return dead;
+}
+// env_mujoco.py:128-150 after the 50 substeps.  cause: 0 running, 1 success, 2 time-out, 3 singular exit, 4 drop / -20 exit.
+// Returns 0 when the result is not finite (caller: NaN guard).
+JHD int step_end(const JacoCfg& cfg, FastSim& s, int env_id, float* obs, float* reward, int* done, int* succ, float* wb, int* cause) {
+  get_observation(cfg, s, env_id, obs);
+  float r = get_reward(cfg, s), bonus, w; int sc, d;
+  s.current_steps += 1;
+  if (s.current_steps < cfg.task_max_steps) d = terminal_inspection(cfg, s, &bonus, &w, &sc);
+  else { d = 1; bonus = -10; w = 0; sc = 0; }
+  *cause = !d ? 0 : (sc ? 1 : (s.current_steps >= cfg.task_max_steps ? 2 : (bonus == -1.0f ? 3 : (bonus == -20.0f ? 4 : 5))));
+  r += bonus;
+  if (!(r == r)) return 0;
+  *reward = r; *done = d; *succ = sc; *wb = w;
+  s.rng_counter += 1;
+  return 1;
+}
 
+// One env step on the fast path, all 50 substeps in one call (CPU harness and diagnostics; the production kernels run
+// the same pieces substep by substep, jaco_pipe.cuh).  Returns FAST_OK with all outputs written into s / obs / ..., or
+// FAST_BAIL (reason bits in *why) with s in an unspecified state -- the caller must not store it.
+// COOP = true: nothing bails for contact reasons; environments that need the general contact handling get it from
+// the warp-cooperative path (jaco_coop.cuh) through the per-warp workspace ws, substep by substep.  All lanes of a
+// warp must then call this function together (lanes without an environment pass active = false).
+template <bool COOP>
+JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* action, float* obs, float* reward, int* done, int* succ, float* wb, int* why,
+                      CoopWS* ws = nullptr, bool active = true, int* cause = nullptr) {
+  *why = 0;
+  int anyB = 0;
+  int dead = 0;  // COOP: bail reason latched, the thread keeps pace with its warp until the step ends
+  if (!step_begin(cfg, s, action, COOP ? OSC_INLINE : OSC_BAIL, nullptr)) { *why = BAIL_OSC; if (!COOP) return FAST_BAIL; dead |= BAIL_OSC; }
+  SceneBoxes sb;
+  scene_static(sb);
   for (int it = 0; it < 50; it++) {
     JSYNC1();
-    // ---- joint limits (mj_instantiateLimit): any active limit row leaves the fast regime
-    int bail = 0;
-#pragma unroll
-    for (int k = 0; k < 9; k++)
-      if (m.ch_limited[k] && (s.qpos[k] - m.ch_range[k][0] < 0 || m.ch_range[k][1] - s.qpos[k] < 0)) bail |= BAIL_LIMIT;
-    // ---- free boxes at the current state
-    FreeBody fo, fd;
-    free_body_setup(10, FG_OBJ, s.qpos + 9, s.qvel + 9, fo);
-    JSYNC3();
-    free_body_setup(11, FG_DEST, s.qpos + 16, s.qvel + 15, fd);
-    JSYNC3();
-    v3copy(s.objp, fo.x);
-    v3copy(sb.op, fo.gp); v3copy(sb.dp, fd.gp);
-#pragma unroll
-    for (int i = 0; i < 9; i++) { sb.oR[i] = fo.gR[i]; sb.dR[i] = fd.gR[i]; }
-    // ---- scene contacts
-    Con4 co, cd;
-    {  // object: holder (box-box face) or floor (plane-box); both at once or anything else -> general path
-      Con4 cf; con4_clear(cf);
-      float dz[3]; v3sub(dz, fo.gp, GF.pos);
-      float pn[3] = {GF.R[2], GF.R[5], GF.R[8]};
-      if (v3dot(dz, pn) - m.geoms[FG_OBJ].rbound <= m.pairs[FP_FLOOR_OBJ].margin)
-        fast_plane_box(FP_FLOOR_OBJ, GF.pos, GF.R, fo.gp, fo.gR, sb.oh, m.pairs[FP_FLOOR_OBJ].margin, cf);
-      int rc = fast_box_box_face(FP_HOLDER_OBJ, sb.hp, sb.hR, sb.hh, fo.gp, fo.gR, sb.oh, m.pairs[FP_HOLDER_OBJ].margin, co);
-      if (rc < 0) bail |= BAIL_OBJ;
-      int nf = con4_count(cf), nh = rc > 0 ? con4_count(co) : 0;
-      if (nf > 0 && nh > 0) bail |= BAIL_OBJ;
-      if (nh == 0) co = cf;
-      float dd[3]; v3sub(dd, fd.gp, fo.gp);
-      if (!(v3norm(dd) > m.geoms[FG_DEST].rbound + m.geoms[FG_OBJ].rbound + m.pairs[FP_DEST_OBJ].margin)) bail |= BAIL_OBJ;
-    }
-    JSYNC3();
-    fast_plane_box(FP_FLOOR_DEST, GF.pos, GF.R, fd.gp, fd.gR, sb.dh, m.pairs[FP_FLOOR_DEST].margin, cd);
-    JSYNC2();
-    // ---- chain dynamics at (q, v), reference point = EE position of the previous forward
-    float O[3]; v3copy(O, s.eepos);
-    fast_chain<true>(s.qpos, s.qvel, O, &sb, c);
-    bail |= c.near;
+    SubFwd f;
+    sub_forward<COOP>(s, sb, it, f);
+    const int bail = f.bail;
     if (!COOP && bail) { *why = bail; return FAST_BAIL; }
-    JSYNC2();
-    // ---- actuation + smooth forces of the chain (fwd_actuation, mj_passive)
-    float fsm[9], acc[9];
-    const float gcmd = ramp_value(s, it);
-#pragma unroll
-    for (int i = 0; i < 6; i++) fsm[i] = fminf(fmaxf(s.u[i], m.motor_fr[i][0]), m.motor_fr[i][1]) - c.bias[i] - m.ch_damping[i] * s.qvel[i];
-#pragma unroll
-    for (int i = 0; i < 3; i++) {
-      const float* A = m.finger_act[i];
-      float cc = fminf(fmaxf(gcmd, A[1]), A[2]);
-      float f = A[0] * cc - A[0] * s.qpos[6 + i];
-      fsm[6 + i] = fminf(fmaxf(f, A[3]), A[4]) - c.bias[6 + i] - m.ch_damping[6 + i] * s.qvel[6 + i];
-    }
     // ---- general contact handling on demand (warp-cooperative)
     int solved = 0;   // bit mask of the blocks (1 chain, 2 object, 4 dest) the cooperative path solved for this env
     float qacc_g[JACO_NV], fcon_g[JACO_NV];
@@ -1180,7 +1276,7 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
       const int flags = ((bail & (BAIL_OBJ | BAIL_DEST)) ? 0 : COOP_SIMPLE_OBJ) | ((bail & (BAIL_LIMIT | BAIL_OBJ | BAIL_DEST)) ? COOP_FORCE_B : 0);
       // own broad + narrow phase over the arm pairs; stage B only for lanes with something to solve
       LocalSink ks; ks.ncon = 0;
-      if (!(JACO_TIMING_SKIP & 2) && need && (bail & (BAIL_HAND | BAIL_FOREARM))) fast_arm_collide(c, fo, fd, ks);
+      if (!(JACO_TIMING_SKIP & 2) && need && (bail & (BAIL_HAND | BAIL_FOREARM))) fast_arm_collide(f.c, f.fo, f.fd, ks);
       const bool needB = !(JACO_TIMING_SKIP & 1) && need && (ks.ncon > 0 || (flags & COOP_FORCE_B));
       FAST_WSTAT(0);
       if (need) { FAST_WSTAT(1); if (bail & BAIL_LIMIT) FAST_WSTAT(8); if (bail & (BAIL_HAND | BAIL_FOREARM)) FAST_WSTAT(9); if (bail & (BAIL_OBJ | BAIL_DEST)) FAST_WSTAT(10); }
@@ -1201,7 +1297,7 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
       for (int base = 0; base < ntask; base += nwarps) {
         const bool mine = slot >= base && slot < base + nwarps;
         JPROF_T(t1);
-        if (mine) { CoopWS& wt = wsbase[slot - base]; coop_publish(wt, s, c, fo, fd, fsm, it == 49); coop_publish_contacts(wt, ks, flags); }
+        if (mine) { CoopWS& wt = wsbase[slot - base]; coop_publish(wt, s, f.c, f.fo, f.fd, f.fsm, it == 49); coop_publish_contacts(wt, ks, flags); }
         __syncthreads();
         JPROF_T(t2);
         if (base + mywarp < ntask) {
@@ -1220,8 +1316,8 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
       }
 #else
       if (needB) {
-        FAST_WSTAT(2);
-        coop_publish(*ws, s, c, fo, fd, fsm, it == 49); coop_publish_contacts(*ws, ks, flags);
+        FAST_WSTAT(2); anyB = 1;
+        coop_publish(*ws, s, f.c, f.fo, f.fd, f.fsm, it == 49); coop_publish_contacts(*ws, ks, flags);
         solved = coop_stageB(*ws);
         if (solved) { FAST_WSTAT(3); FAST_WSTAT_ADD(4, ws->iters); FAST_WSTAT_ADD(5, ws->ncon); if (solved & 1) FAST_WSTAT(6); if (ws->ncon > 0) FAST_WSTAT(7);
           for (int i = 0; i < JACO_NV; i++) { qacc_g[i] = ws->qacc[i]; fcon_g[i] = ws->fcon[i]; } if (it == 49) s.touch_now = touch_class(ws->touch); }
@@ -1229,31 +1325,12 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
 #endif
     }
     JSYNC2();
-    if (it == 49) {  // what the next env step needs from this forward
-      if (solved & 1) { for (int i = 0; i < 9; i++) s.warm[i] = qacc_g[i]; }
-      else { chain_solve(c, 0.0f, fsm, acc); for (int i = 0; i < 9; i++) s.warm[i] = acc[i]; }
-#pragma unroll
-      for (int i = 0; i < 9; i++) { s.lagq[i] = s.qpos[i]; s.lagv[i] = s.qvel[i]; }
-    }
-    // ---- mj_Euler, chain (implicit joint damping)
-    if (solved & 1) { for (int i = 0; i < 9; i++) fsm[i] += fcon_g[i]; }
-    if (!chain_solve(c, h, fsm, acc)) { *why = BAIL_NAN; if (!COOP) return FAST_BAIL; dead |= BAIL_NAN; }
-    JSYNC3();
-#pragma unroll
-    for (int i = 0; i < 9; i++) { s.qvel[i] += h * acc[i]; s.qpos[i] += h * s.qvel[i]; }
-    // ---- free boxes: contact solve + Euler
-    if (solved & 2) free_integrate(fo, qacc_g + 9, fcon_g + 9, s.qpos + 9, s.qvel + 9, s.warm + 9);
-    else fast_free_step(fo, co, s.qpos + 9, s.qvel + 9, s.warm + 9);
-    JSYNC3();
-    if (solved & 4) free_integrate(fd, qacc_g + 15, fcon_g + 15, s.qpos + 16, s.qvel + 15, s.warm + 15);
-    else fast_free_step(fd, cd, s.qpos + 16, s.qvel + 15, s.warm + 15);
-    JSYNC2();
-    // ---- controller output for the next substep from this forward's mjData and the fresh joint velocity
-    v3copy(s.eepos, c.eepos);
-#pragma unroll
-    for (int i = 0; i < 4; i++) s.eeq[i] = c.eeq[i];
-    if (it < 49) { if (!fast_osc(c, s.tq, s.target, s.qvel, s.u, COOP)) { *why = BAIL_OSC; if (!COOP) return FAST_BAIL; dead |= BAIL_OSC; } }
+    int osc_ret;
+    const int dd = sub_finish<COOP>(s, f, it, solved, qacc_g, fcon_g, COOP ? OSC_INLINE : OSC_BAIL, nullptr, &osc_ret);
+    if (dd) { *why = dd; if (!COOP) return FAST_BAIL; dead |= dd; }
   }
+  if (anyB) FAST_WSTAT(14);
+  (void)anyB;
   if (dead) { *why = dead; return FAST_BAIL; }
   bool bad = false;
 #pragma unroll
@@ -1261,15 +1338,9 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
 #pragma unroll
   for (int k = 0; k < JACO_NV; k++) bad = bad || !(fabsf(s.qvel[k]) < 1e6f);
   if (bad) { *why = BAIL_NAN; return FAST_BAIL; }
-  get_observation(cfg, s, env_id, obs);
-  float r = get_reward(cfg, s), bonus, w; int sc, d;
-  s.current_steps += 1;
-  if (s.current_steps < cfg.task_max_steps) d = terminal_inspection(cfg, s, &bonus, &w, &sc);
-  else { d = 1; bonus = -10; w = 0; sc = 0; }
-  r += bonus;
-  if (!(r == r)) { *why = BAIL_NAN; return FAST_BAIL; }
-  *reward = r; *done = d; *succ = sc; *wb = w;
-  s.rng_counter += 1;
+  int cz = 0;
+  if (!step_end(cfg, s, env_id, obs, reward, done, succ, wb, &cz)) { *why = BAIL_NAN; return FAST_BAIL; }
+  if (cause) *cause = cz;
   return FAST_OK;
 }
 
@@ -1290,7 +1361,7 @@ JHD void fast_load(const float* state, int N, int i, FastSim& s) {
   for (int k = 0; k < 3; k++) { s.obj_goal[k] = ST(A + AUX_OBJ_GOAL + k); s.dest_goal[k] = ST(A + AUX_DEST_GOAL + k); }
 #pragma unroll
   for (int k = 0; k < 6; k++) s.reach_goal[k] = ST(A + AUX_REACH_GOAL + k);
-  s.rng_counter = (uint32_t)ST(A + AUX_RNG); s.touch_index = (int)ST(A + AUX_TOUCH);
+  s.rng_counter = (uint32_t)ST(A + AUX_RNG) + ((uint32_t)ST(A + AUX_RNG_HI) << 24); s.touch_index = (int)ST(A + AUX_TOUCH);
 #pragma unroll
   for (int k = 0; k < JACO_NV; k++) s.warm[k] = ST(A + AUX_WARM + k);
 #pragma unroll
@@ -1307,7 +1378,7 @@ JHD void fast_store(float* state, int N, int i, const FastSim& s) {
   for (int k = 0; k < 6; k++) ST(A + AUX_TARGET + k) = s.target[k];
   ST(A + AUX_GRIP) = s.grip; ST(A + AUX_ACTION_IN) = (float)s.action_in; ST(A + AUX_PICKED) = (float)s.picked;
   ST(A + AUX_CUR_STEPS) = (float)s.current_steps; ST(A + AUX_NUM_EPISODES) = (float)s.num_episodes;
-  ST(A + AUX_RNG) = (float)s.rng_counter; ST(A + AUX_TOUCH) = (float)s.touch_index;
+  ST(A + AUX_RNG) = (float)(s.rng_counter & 0xFFFFFFu); ST(A + AUX_RNG_HI) = (float)(s.rng_counter >> 24); ST(A + AUX_TOUCH) = (float)s.touch_index;
 #pragma unroll
   for (int k = 0; k < JACO_NV; k++) ST(A + AUX_WARM + k) = s.warm[k];
 #pragma unroll
@@ -1329,15 +1400,17 @@ JHD int entry_step_fast(const JacoCfg& cfg, float* state, int N, int i, int env_
   fast_load(state, N, i, s);
   float obs[JACO_NOBS], r, w; int d, sc;
   *needs_reset = 0;
-  int rc = fast_env_step<COOP>(cfg, s, env_id, action_row, obs, &r, &d, &sc, &w, why, ws, active);
+  int cause = 0;
+  int rc = fast_env_step<COOP>(cfg, s, env_id, action_row, obs, &r, &d, &sc, &w, why, ws, active, &cause);
   if (!active) return FAST_OK;
   if (rc != FAST_OK) return FAST_BAIL;
   s.accum_rew += r;
   local_stats[STAT_STEPS] += 1;
   if (d) {
     local_stats[STAT_EPISODES] += 1; local_stats[STAT_SUCCESS] += sc; local_stats[STAT_RETURN] += s.accum_rew; local_stats[STAT_LENGTH] += s.current_steps;
-    if (s.current_steps >= cfg.task_max_steps) local_stats[STAT_TIMEOUT] += 1;
-    else if (r - get_reward(cfg, s) == -1.0f) local_stats[STAT_SINGULAR] += 1;
+    if (cause == 2) local_stats[STAT_TIMEOUT] += 1;
+    else if (cause == 3) local_stats[STAT_SINGULAR] += 1;
+    else if (cause == 4) local_stats[STAT_DROP] += 1;
     if (auto_reset) *needs_reset = 1;
   }
   fast_store(state, N, i, s);

@@ -1,7 +1,8 @@
-// jaco_kernels.cu -- CUDA kernels (sm_100a) and the C ABI of libjaco_b200.so (include/jaco_b200.h).
-// One thread advances one environment through a whole env step (50 fused physics substeps); state is SoA in
-// HBM so every load/store of a warp is one coalesced 128-byte line per state row; model constants sit in
-// __constant__ memory (uniform broadcast reads).  See DESIGN.md for the layout and the roofline.
+// jaco_kernels.cu -- the C ABI of libjaco_b200.so (include/jaco_b200.h) and the general-path kernels.
+// The production env step is the per-substep pipeline of jaco_kernel_pipe.cu; the kernels here are the general
+// thread-per-env path (reset, raw mj_step for parity injection, and the work-list kernel that re-runs the few envs the
+// pipeline hands back).  State is SoA in HBM so every load/store of a warp is one coalesced 128-byte line per state
+// row; model constants sit in __constant__ memory (uniform broadcast reads).  See DESIGN.md.
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <string.h>
@@ -16,14 +17,17 @@ struct jaco_sim_handle {
   int n, device, env_offset;
   JacoCfg cfg;
   float* state;       // [JACO_NSTATE][n]
-  float* stats;       // [16]
+  double* stats;      // [16] (double on the device: a float counter stops counting at 2^24)
   float *s_action, *s_obs, *s_reward, *s_wb; unsigned char *s_done, *s_succ;  // staging for jaco_step_host
-  int use_fast;        // model matches the structure jaco_fast.cuh is specialised to
-  int* worklist;       // [2][n] env indices: row 0 = bailed out of the fast kernel, row 1 = finished episodes to reset
+  int use_fast;        // 3 pipeline (production); diagnostic builds: 2 fused hybrid kernel, 1 fused fast kernel, 0 general kernel
+  int* worklist;       // [2][n] env indices: row 0 = handed back by the pipeline, row 1 = finished episodes to reset
   int* counters;       // [16]: 0 n_bail, 1 n_reset, 2.. bail-reason histogram (cumulative, diagnostics)
+  JacoPipe pipe;
+  JacoModel* model;    // host copy: the model symbols are per library, a handle re-uploads them when another handle used them last
   long long launches;
   char err[256];
 };
+static jaco_sim_handle* g_model_owner = nullptr;   // handle whose model the __constant__ / __device__ symbols hold
 
 __global__ void __launch_bounds__(JACO_BLOCK) jaco_reset_kernel(JacoCfg cfg, float* state, int N, int env_offset, const unsigned char* mask, float* obs) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -33,7 +37,7 @@ __global__ void __launch_bounds__(JACO_BLOCK) jaco_reset_kernel(JacoCfg cfg, flo
 }
 
 __global__ void __launch_bounds__(JACO_BLOCK) jaco_step_kernel(JacoCfg cfg, float* state, int N, int env_offset, const float* action, float* obs, float* reward,
-                                                               unsigned char* done, unsigned char* succ, float* wb, float* term_obs, int auto_reset, float* gstats) {
+                                                               unsigned char* done, unsigned char* succ, float* wb, float* term_obs, int auto_reset, double* gstats) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   float local[16];
 #pragma unroll
@@ -52,9 +56,9 @@ __global__ void __launch_bounds__(JACO_BLOCK) jaco_step_kernel(JacoCfg cfg, floa
 
 #define JACO_LIST_BLOCK 32
 
-// general path over the bail list, then the general reset over the finished-episode list
-__global__ void __launch_bounds__(JACO_LIST_BLOCK) jaco_step_list_kernel(JacoCfg cfg, float* state, int N, int env_offset, const float* action, float* obs, float* reward,
-                                                                         unsigned char* done, unsigned char* succ, float* wb, float* term_obs, int auto_reset, float* gstats,
+// general path over the hand-back list (from the pre-step snapshot), then the general reset over the finished-episode list
+__global__ void __launch_bounds__(JACO_LIST_BLOCK) jaco_step_list_kernel(JacoCfg cfg, float* state, const float* state_prev, int N, int env_offset, const float* action, float* obs, float* reward,
+                                                                         unsigned char* done, unsigned char* succ, float* wb, float* term_obs, int auto_reset, double* gstats,
                                                                          const int* worklist, const int* counters) {
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   const int nb = counters[0], nr = counters[1];
@@ -64,6 +68,8 @@ __global__ void __launch_bounds__(JACO_LIST_BLOCK) jaco_step_list_kernel(JacoCfg
   for (int k = 0; k < 16; k++) local[k] = 0;
   if (t < nb) {
     int i = worklist[t];
+    if (state_prev) for (int r = 0; r < JACO_NSTATE; r++) state[(size_t)r * N + i] = state_prev[(size_t)r * N + i];
+    local[STAT_FALLBACK] += 1;
     float a[JACO_NACT];
 #pragma unroll
     for (int k = 0; k < JACO_NACT; k++) a[k] = action[(size_t)i * JACO_NACT + k];
@@ -73,6 +79,7 @@ __global__ void __launch_bounds__(JACO_LIST_BLOCK) jaco_step_list_kernel(JacoCfg
     reward[i] = r; done[i] = d; succ[i] = sc; wb[i] = w;
   } else if (t < nb + nr) {
     int i = worklist[N + (t - nb)];
+    local[STAT_GENRESET] += 1;
     entry_reset(cfg, state, N, i, env_offset + i, obs + (size_t)i * JACO_NOBS);
   }
   block_stats_flush(local, gstats);
@@ -98,6 +105,11 @@ __global__ void jaco_scatter_kernel(float* state, int N, int row0, int nrows, co
   for (int r = 0; r < nrows; r++) state[(size_t)(row0 + r) * N + i] = in[(size_t)i * nrows + r];
 }
 
+__global__ void jaco_stats_read_kernel(double* stats, float* out, int clear) {
+  int k = threadIdx.x;
+  if (k < JACO_NSTATS) { out[k] = (float)stats[k]; if (clear) stats[k] = 0.0; }
+}
+
 // FP32 FMA peak micro-benchmark: the denominator of the step kernel's compute roofline
 __global__ void __launch_bounds__(256) jaco_fma_peak_kernel(float* out, int iters) {
   float x = 1.0f + 1e-7f * threadIdx.x, y = 1e-9f * blockIdx.x;
@@ -118,6 +130,21 @@ __global__ void __launch_bounds__(256) jaco_fma_peak_kernel(float* out, int iter
     if (e_ != cudaSuccess) { snprintf(h->err, sizeof h->err, "%s: %s", #call, cudaGetErrorString(e_)); return JACO_ECUDA; } \
   } while (0)
 
+// The model symbols (__constant__ / __device__, one copy per translation unit) belong to the library, not to a handle:
+// a handle whose model is not the one currently uploaded re-uploads it, stream-ordered, before it launches anything.
+static cudaError_t upload_model(jaco_sim_handle* h) {
+  if (g_model_owner == h) return cudaSuccess;
+  cudaError_t e = cudaMemcpyToSymbol(c_jaco_model, h->model, sizeof(JacoModel));
+  if (e == cudaSuccess) e = cudaMemcpyToSymbol(g_jaco_model_dev, h->model, sizeof(JacoModel));
+  if (e == cudaSuccess) e = jaco_pipe_upload_model(h->model);
+#ifdef JACO_DIAG
+  if (e == cudaSuccess) e = jaco_fast_upload_model(h->model);
+  if (e == cudaSuccess) e = jaco_coop_upload_model(h->model);
+#endif
+  if (e == cudaSuccess) g_model_owner = h;
+  return e;
+}
+
 extern "C" {
 
 int jaco_create(const void* model_blob, size_t nbytes, int n_envs, int task_id, int variant, int device, uint64_t seed, int env_offset, jaco_handle* out) {
@@ -130,36 +157,37 @@ int jaco_create(const void* model_blob, size_t nbytes, int n_envs, int task_id, 
   h->cfg.task = task_id; h->cfg.variant = variant & 15; h->cfg.obs_mode = (variant >> 4) & 15; h->cfg.seed = seed;
   h->cfg.task_max_steps = (task_id == JACO_REACHING || task_id == JACO_GRASPING) ? 500 : ((task_id == JACO_PICKING || task_id == JACO_PLACING) ? 700 : 1200);
   CK(cudaSetDevice(device));
-  JacoModel* m = new JacoModel();
-  jaco_model_from_blob((const double*)model_blob, m);
-  cudaError_t e = cudaMemcpyToSymbol(c_jaco_model, m, sizeof(JacoModel));
-  if (e == cudaSuccess) e = cudaMemcpyToSymbol(g_jaco_model_dev, m, sizeof(JacoModel));
-  const bool fast_ok = fast_model_ok(*m);
-  if (e == cudaSuccess) e = jaco_fast_upload_model(m);
-  if (e == cudaSuccess) e = jaco_coop_upload_model(m);
-  delete m;
-  CK(e);
+  h->model = new JacoModel();
+  jaco_model_from_blob((const double*)model_blob, h->model);
+  CK(upload_model(h));
   CK(cudaMalloc(&h->state, sizeof(float) * JACO_NSTATE * (size_t)n_envs));
   CK(cudaMemset(h->state, 0, sizeof(float) * JACO_NSTATE * (size_t)n_envs));
-  h->use_fast = fast_ok ? 1 : 0;
-  if (h->use_fast) h->use_fast = 2;                      /* default: hybrid fast + warp-cooperative kernel */
-  if (getenv("JACO_NO_COOP") && h->use_fast) h->use_fast = 1;  /* diagnostics: fast kernel with bail-out to the general list kernel */
-  if (getenv("JACO_NO_FAST")) h->use_fast = 0;           /* diagnostics: general thread-per-env kernel only */
+  h->use_fast = fast_model_ok(*h->model) ? 3 : 0;        /* production: the per-substep pipeline; a model without the hard-wired scene structure runs the general kernel */
+#ifdef JACO_DIAG   /* diagnostic builds only: the round-1 fused kernels for A/B timing and cross-checks */
+  if (getenv("JACO_FUSED") && h->use_fast) h->use_fast = 2;
+  if (getenv("JACO_NO_COOP") && h->use_fast) h->use_fast = 1;
+  if (getenv("JACO_NO_FAST")) h->use_fast = 0;
+#endif
   CK(cudaMalloc(&h->worklist, sizeof(int) * 2 * (size_t)n_envs));
   CK(cudaMalloc(&h->counters, sizeof(int) * 16));
   CK(cudaMemset(h->counters, 0, sizeof(int) * 16));
-  CK(cudaMalloc(&h->stats, sizeof(float) * JACO_NSTATS));
-  CK(cudaMemset(h->stats, 0, sizeof(float) * JACO_NSTATS));
+  CK(cudaMalloc(&h->stats, sizeof(double) * JACO_NSTATS));
+  CK(cudaMemset(h->stats, 0, sizeof(double) * JACO_NSTATS));
   CK(cudaFuncSetAttribute(jaco_step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 0));
   CK(cudaFuncSetAttribute(jaco_reset_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 0));
+  CK(jaco_pipe_create(&h->pipe, n_envs, device));
   return JACO_OK;
 }
 
 void jaco_destroy(jaco_handle h) {
   if (!h) return;
   cudaSetDevice(h->device);
+  cudaDeviceSynchronize();
+  jaco_pipe_destroy(&h->pipe);
   cudaFree(h->state); cudaFree(h->stats); cudaFree(h->worklist); cudaFree(h->counters);
   cudaFree(h->s_action); cudaFree(h->s_obs); cudaFree(h->s_reward); cudaFree(h->s_wb); cudaFree(h->s_done); cudaFree(h->s_succ);
+  if (g_model_owner == h) g_model_owner = nullptr;
+  delete h->model;
   delete h;
 }
 const char* jaco_last_error(jaco_handle h) { return h ? h->err : "null handle"; }
@@ -168,14 +196,14 @@ int jaco_debug_counters(jaco_handle h, int* out16) {  /* host copy of the work-l
   CK(cudaMemcpy(out16, h->counters, 16 * sizeof(int), cudaMemcpyDeviceToHost));
   return JACO_OK;
 }
-int jaco_debug_prof(unsigned long long* out16) { return jaco_coop_prof(out16); }
 int jaco_n_envs(jaco_handle h) { return h ? h->n : 0; }
-long long jaco_launch_count(jaco_handle h) { return h ? h->launches : 0; }
+long long jaco_launch_count(jaco_handle h) { return h ? h->launches + h->pipe.launches : 0; }
 
 static inline int nblocks(int n) { return (n + JACO_BLOCK - 1) / JACO_BLOCK; }
 
 int jaco_reset(jaco_handle h, const uint8_t* mask, float* obs, void* stream) {
   if (!h) return JACO_EINVAL;
+  CK(upload_model(h));
   jaco_reset_kernel<<<nblocks(h->n), JACO_BLOCK, 0, (cudaStream_t)stream>>>(h->cfg, h->state, h->n, h->env_offset, mask, obs);
   h->launches++;
   CK(cudaGetLastError());
@@ -185,14 +213,23 @@ int jaco_reset(jaco_handle h, const uint8_t* mask, float* obs, void* stream) {
 int jaco_step(jaco_handle h, const float* action, float* obs, float* reward, uint8_t* done, uint8_t* succ, float* wb, float* term_obs, int auto_reset, void* stream) {
   if (!h || !action || !obs || !reward || !done || !succ || !wb) return JACO_EINVAL;
   cudaStream_t st = (cudaStream_t)stream;
-  if (h->use_fast) {
+  CK(upload_model(h));
+  JacoStepArgs A = {h->cfg, h->state, h->n, h->env_offset, action, obs, reward, done, succ, wb, term_obs, auto_reset, h->stats, h->worklist, h->counters};
+  const int nlist = (h->n + JACO_LIST_BLOCK - 1) / JACO_LIST_BLOCK;
+  if (h->use_fast == 3) {
     CK(cudaMemsetAsync(h->counters, 0, 2 * sizeof(int), st));
-    JacoStepArgs A = {h->cfg, h->state, h->n, h->env_offset, action, obs, reward, done, succ, wb, term_obs, auto_reset, h->stats, h->worklist, h->counters};
+    CK(jaco_pipe_step(&h->pipe, A, h->stats, st));
+    jaco_step_list_kernel<<<nlist, JACO_LIST_BLOCK, 0, st>>>(h->cfg, h->state, h->pipe.state_prev, h->n, h->env_offset, action, obs, reward, done, succ, wb,
+                                                           term_obs, auto_reset, h->stats, h->worklist, h->counters);
+    h->launches += 1;
+#ifdef JACO_DIAG
+  } else if (h->use_fast) {
+    CK(cudaMemsetAsync(h->counters, 0, 2 * sizeof(int), st));
     CK(h->use_fast == 2 ? jaco_coop_launch(A, st) : jaco_fast_launch(A, st));
-    if (!getenv("JACO_FAST_ONLY"))  /* timing experiments only: skips the general pass, results are then incomplete */
-    jaco_step_list_kernel<<<(h->n + JACO_LIST_BLOCK - 1) / JACO_LIST_BLOCK, JACO_LIST_BLOCK, 0, st>>>(h->cfg, h->state, h->n, h->env_offset, action, obs, reward, done, succ, wb,
-                                                                                                   term_obs, auto_reset, h->stats, h->worklist, h->counters);
+    jaco_step_list_kernel<<<nlist, JACO_LIST_BLOCK, 0, st>>>(h->cfg, h->state, nullptr, h->n, h->env_offset, action, obs, reward, done, succ, wb,
+                                                           term_obs, auto_reset, h->stats, h->worklist, h->counters);
     h->launches += 2;
+#endif
   } else {
     jaco_step_kernel<<<nblocks(h->n), JACO_BLOCK, 0, st>>>(h->cfg, h->state, h->n, h->env_offset, action, obs, reward, done, succ, wb, term_obs, auto_reset, h->stats);
     h->launches++;
@@ -244,6 +281,7 @@ int jaco_set_state(jaco_handle h, const float* qpos, const float* qvel, const fl
 }
 int jaco_debug_substep(jaco_handle h, const float* ctrl, int32_t* ncon, float* sensordata, float* qacc, void* stream) {
   if (!h || !ctrl) return JACO_EINVAL;
+  CK(upload_model(h));
   jaco_substep_kernel<<<nblocks(h->n), JACO_BLOCK, 0, (cudaStream_t)stream>>>(h->state, h->n, ctrl, ncon, sensordata, qacc);
   h->launches++;
   CK(cudaGetLastError());
@@ -251,9 +289,9 @@ int jaco_debug_substep(jaco_handle h, const float* ctrl, int32_t* ncon, float* s
 }
 int jaco_stats(jaco_handle h, float* out16, int clear, void* stream) {
   if (!h || !out16) return JACO_EINVAL;
-  cudaStream_t st = (cudaStream_t)stream;
-  CK(cudaMemcpyAsync(out16, h->stats, sizeof(float) * JACO_NSTATS, cudaMemcpyDeviceToDevice, st));
-  if (clear) CK(cudaMemsetAsync(h->stats, 0, sizeof(float) * JACO_NSTATS, st));
+  jaco_stats_read_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(h->stats, out16, clear);
+  h->launches++;
+  CK(cudaGetLastError());
   return JACO_OK;
 }
 

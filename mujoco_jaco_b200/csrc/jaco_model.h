@@ -23,7 +23,8 @@ enum { JACO_GEOM_PLANE = 0, JACO_GEOM_BOX = 1, JACO_GEOM_CAPSULE = 2 };
 enum {
   AUX_TARGET = 0, AUX_GRIP = 6, AUX_ACTION_IN = 7, AUX_PICKED = 8, AUX_CUR_STEPS = 9, AUX_NUM_EPISODES = 10,
   AUX_OBJ_GOAL = 11, AUX_DEST_GOAL = 14, AUX_REACH_GOAL = 17, AUX_RNG = 23, AUX_TOUCH = 24, AUX_WARM = 25,
-  AUX_LAGQ = 46, AUX_LAGV = 55, AUX_ACCUM_REW = 64, AUX_EPLEN = 65
+  AUX_LAGQ = 46, AUX_LAGV = 55, AUX_ACCUM_REW = 64, AUX_EPLEN = 65,
+  AUX_RNG_HI = 66   // Philox step counter = AUX_RNG (low 24 bits) + 2^24 * AUX_RNG_HI: exact in float rows for all uint32
 };
 
 struct JacoGeom { int type, body; float pos[3], R[9], size[3], rbound; };

@@ -1414,7 +1414,7 @@ JHD float get_reward(const JacoCfg& cfg, const S& s) {  // util:312-446
     float d[3]; v3sub(d, s.gripper_pose, s.reach_goal);
     float dist = v3norm(d), ang = reach_ang_diff(s);
     float r = 5 * expf(-dist) / 2 + 2 * expf(-ang / (JPI / 6)) / (2 * (dist * 15 + 1));
-    float w[3]; v3sub(w, s.eepos, MDL.base_pos);
+    float w[3]; v3sub(w, s.eepos, cfg.variant == 0 ? MDL.base_pos : MDL.base_link_pos);   // cis:42,409
     float wb = v3norm(w);
     if (wb < 0.15f) r -= 0.15f - wb;
     if (s.gripper_pose[2] < 0.1f) r -= 0.1f - s.gripper_pose[2];
@@ -1445,7 +1445,7 @@ template <class S>
 JHD int terminal_inspection(const JacoCfg& cfg, S& s, float* bonus, float* wb, int* succ) {  // util:492-600
   s.num_episodes += 1;
   float d[3]; *succ = 0; *bonus = 0;
-  v3sub(d, s.eepos, MDL.base_pos); *wb = v3norm(d);
+  v3sub(d, s.eepos, cfg.variant == 0 ? MDL.base_pos : MDL.base_link_pos); *wb = v3norm(d);   // util:35,499; cis:42,590
   const float* op = obj_pos(s);
   float dx = s.dest_goal[0] - op[0], dy = s.dest_goal[1] - op[1], dest_diff = sqrtf(dx * dx + dy * dy);
   float q2 = s.qpos[2];
@@ -1517,14 +1517,16 @@ JHD float round_half(float v) {  // value after a round trip through np.float16 
   mnt = rintf(mnt * 2048.0f) / 2048.0f;
   return ldexpf(mnt, ex);
 }
-// env_mujoco.py:99-102 -> util:92-174.  Leaves mjData (the JacoSim working set) evaluated at the reset state.
-JHD void env_reset(const JacoCfg& cfg, JacoSim& s, int env_id, float* obs) {
+// sim.reset() + _create_init_angle + __sample_goal + set_dest_xyz (util:92-103,176-221; mujoco.py:229-237): everything of
+// reset() that precedes the first mj_forward.  Shared by the general reset (env_reset) and the pipeline's in-kernel reset
+// (jaco_fast.cuh fast_reset); S = JacoSim or FastSim.
+template <class S>
+JHD void reset_sample(const JacoCfg& cfg, S& s, int env_id) {
   const JacoModel& m = MDL;
   s.current_steps = 0;
   for (int k = 0; k < 9; k++) s.qpos[k] = m.ch_ref[k];
   for (int f = 0; f < 2; f++) for (int i = 0; i < 7; i++) s.qpos[9 + 7 * f + i] = m.free_qpos0[f][i];
   for (int i = 0; i < JACO_NV; i++) { s.qvel[i] = 0; s.warm[i] = 0; }
-  for (int i = 0; i < JACO_NU; i++) s.ctrl[i] = 0;
   s.action_in = 0; s.picked = 0; s.grip = 0.6f; s.ramp0 = s.ramp1 = 0.6f; s.touch_index = 0; s.num_episodes = 0;
   float ia[6];
   if (cfg.task == JACO_TASK_REACHING || cfg.task == JACO_TASK_PICKING || cfg.task == JACO_TASK_PICKANDPLACE) {
@@ -1551,6 +1553,12 @@ JHD void env_reset(const JacoCfg& cfg, JacoSim& s, int env_id, float* obs) {
   s.dest_goal[0] = 0.4f + uniab(cfg, s, env_id, 0, 15, -0.05f, 0.05f); s.dest_goal[1] = 0.3f + uniab(cfg, s, env_id, 0, 16, -0.05f, 0.05f); s.dest_goal[2] = 0.3468f;
   if (cfg.variant != 0) for (int i = 0; i < 3; i++) { s.obj_goal[i] += m.base_link_pos[i]; s.dest_goal[i] += m.base_link_pos[i]; }
   if (cfg.variant == 0) { s.qpos[16] = s.dest_goal[0]; s.qpos[17] = s.dest_goal[1]; for (int i = 16; i < JACO_NV; i++) s.qvel[i] = 0; }
+}
+// env_mujoco.py:99-102 -> util:92-174.  Leaves mjData (the JacoSim working set) evaluated at the reset state.
+JHD void env_reset(const JacoCfg& cfg, JacoSim& s, int env_id, float* obs) {
+  const JacoModel& m = MDL;
+  reset_sample(cfg, s, env_id);
+  for (int i = 0; i < JACO_NU; i++) s.ctrl[i] = 0;
   if (cfg.task == JACO_TASK_PLACING) {  // util:106-117: hold the object in the hand for 150 settle substeps
     mj_forward(s, false);
     float p[3], t[3], eul[3], q[4], dp[3], off[3] = {-0.04f, 0, 0}, u[6];
@@ -1581,12 +1589,13 @@ JHD void env_reset(const JacoCfg& cfg, JacoSim& s, int env_id, float* obs) {
 }
 // env_mujoco.py:116-139.  On entry the working set holds the chain quantities at the lagged state
 // (see load path in jaco_kernels.cu); on exit it holds mjData of the last substep's forward.
-JHD void env_step(const JacoCfg& cfg, JacoSim& s, int env_id, const float* action, float* obs, float* reward, int* done, int* succ, float* wb) {
+JHD void env_step(const JacoCfg& cfg, JacoSim& s, int env_id, const float* action, float* obs, float* reward, int* done, int* succ, float* wb, int* cause = nullptr) {
   float a[7], u[6];
   for (int i = 0; i < 7; i++) a[i] = fminf(fmaxf(action[i], -1.0f), 1.0f);
   if (cfg.task == JACO_TASK_REACHING) a[6] = 0;
   take_action(s, a, cfg.variant);
-  if (cfg.task == JACO_TASK_REACHING) { s.grip = 0.6f; s.ramp0 = s.ramp1 = 0.6f; }
+  // 6-D action (util:625-626): grip 0.6 for the observation; the finger servos get gripper_angle_array = zeros (util:37,76-79)
+  if (cfg.task == JACO_TASK_REACHING) { s.grip = 0.6f; s.ramp0 = s.ramp1 = 0.0f; }
   for (int i = 0; i < 50; i++) {
     osc_generate(s, s.qvel, u);
     substep(s, u, i, i == 49);
@@ -1596,6 +1605,8 @@ JHD void env_step(const JacoCfg& cfg, JacoSim& s, int env_id, const float* actio
   s.current_steps += 1;
   if (s.current_steps < cfg.task_max_steps) d = terminal_inspection(cfg, s, &bonus, &w, &sc);
   else { d = 1; bonus = -10; w = 0; sc = 0; }
+  // cause: 0 running, 1 success, 2 time-out, 3 singular exit, 4 drop / -20 exit, 5 other
+  if (cause) *cause = !d ? 0 : (sc ? 1 : (s.current_steps >= cfg.task_max_steps ? 2 : (bonus == -1.0f ? 3 : (bonus == -20.0f ? 4 : 5))));
   *reward = r + bonus; *done = d; *succ = sc; *wb = w;
   s.rng_counter += 1;
 }
@@ -1618,7 +1629,7 @@ JHD void load_env(const float* state, int N, int i, JacoSim& s) {
   for (int k = 0; k < 3; k++) { s.obj_goal[k] = ST(A + AUX_OBJ_GOAL + k); s.dest_goal[k] = ST(A + AUX_DEST_GOAL + k); }
 #pragma unroll
   for (int k = 0; k < 6; k++) s.reach_goal[k] = ST(A + AUX_REACH_GOAL + k);
-  s.rng_counter = (uint32_t)ST(A + AUX_RNG); s.touch_index = (int)ST(A + AUX_TOUCH);
+  s.rng_counter = (uint32_t)ST(A + AUX_RNG) + ((uint32_t)ST(A + AUX_RNG_HI) << 24); s.touch_index = (int)ST(A + AUX_TOUCH);
 #pragma unroll
   for (int k = 0; k < JACO_NV; k++) s.warm[k] = ST(A + AUX_WARM + k);
 #pragma unroll
@@ -1641,7 +1652,7 @@ JHD void store_env(float* state, int N, int i, const JacoSim& s) {
   for (int k = 0; k < 3; k++) { ST(A + AUX_OBJ_GOAL + k) = s.obj_goal[k]; ST(A + AUX_DEST_GOAL + k) = s.dest_goal[k]; }
 #pragma unroll
   for (int k = 0; k < 6; k++) ST(A + AUX_REACH_GOAL + k) = s.reach_goal[k];
-  ST(A + AUX_RNG) = (float)s.rng_counter; ST(A + AUX_TOUCH) = (float)s.touch_index;
+  ST(A + AUX_RNG) = (float)(s.rng_counter & 0xFFFFFFu); ST(A + AUX_RNG_HI) = (float)(s.rng_counter >> 24); ST(A + AUX_TOUCH) = (float)s.touch_index;
 #pragma unroll
   for (int k = 0; k < JACO_NV; k++) ST(A + AUX_WARM + k) = s.warm[k];
 #pragma unroll
@@ -1659,7 +1670,15 @@ JHD void refresh_lagged(JacoSim& s) {
   for (int k = 0; k < 9; k++) { s.qpos[k] = q[k]; s.qvel[k] = v[k]; }
 }
 
-enum { STAT_EPISODES = 0, STAT_SUCCESS = 1, STAT_RETURN = 2, STAT_TIMEOUT = 3, STAT_DROP = 4, STAT_SINGULAR = 5, STAT_NAN = 6, STAT_STEPS = 7, STAT_LENGTH = 8 };
+// episode / workload counters (jaco_stats): 0-8 episode statistics, 9-15 workload and cap counters of the step pipeline
+enum { STAT_EPISODES = 0, STAT_SUCCESS = 1, STAT_RETURN = 2, STAT_TIMEOUT = 3, STAT_DROP = 4, STAT_SINGULAR = 5, STAT_NAN = 6, STAT_STEPS = 7, STAT_LENGTH = 8,
+       STAT_CONCAP = 9,      // env-substeps whose contact list hit JACO_MAXCON / the row pool (contacts were dropped)
+       STAT_ITERCAP = 10,    // Newton solves that stopped on the iteration cap instead of the convergence test
+       STAT_STAGEB = 11,     // env-substeps served by the general (cooperative) contact path
+       STAT_PINV = 12,       // env-substeps whose OSC took the numpy.linalg.pinv branch
+       STAT_FINGEROBJ = 13,  // env-substeps with >= 1 contact between a hand-cluster geom and the object
+       STAT_FALLBACK = 14,   // env steps re-run by the general thread-per-env path (NaN guard / bad pivot)
+       STAT_GENRESET = 15 }; // resets that went through the general reset kernel (hand near the scene at the reset pose)
 
 // per-env entry points shared by the CUDA kernels (jaco_kernels.cu) and the CPU logic harness (tests/)
 JHD void entry_reset(const JacoCfg& cfg, float* state, int N, int i, int env_id, float* obs_row) {
@@ -1680,8 +1699,8 @@ JHD void entry_step(const JacoCfg& cfg, float* state, int N, int i, int env_id, 
 #endif
   load_env(state, N, i, s);
   refresh_lagged(s);
-  float obs[JACO_NOBS], r, w; int d, sc;
-  env_step(cfg, s, env_id, action_row, obs, &r, &d, &sc, &w);
+  float obs[JACO_NOBS], r, w; int d, sc, cause = 0;
+  env_step(cfg, s, env_id, action_row, obs, &r, &d, &sc, &w, &cause);
   bool bad = !(r == r);
   for (int k = 0; k < JACO_NQ; k++) bad = bad || !(fabsf(s.qpos[k]) < 1e6f);
   for (int k = 0; k < JACO_NV; k++) bad = bad || !(fabsf(s.qvel[k]) < 1e6f);
@@ -1690,8 +1709,9 @@ JHD void entry_step(const JacoCfg& cfg, float* state, int N, int i, int env_id, 
   local_stats[STAT_STEPS] += 1;
   if (d) {
     local_stats[STAT_EPISODES] += 1; local_stats[STAT_SUCCESS] += sc; local_stats[STAT_RETURN] += s.accum_rew; local_stats[STAT_LENGTH] += s.current_steps;
-    if (s.current_steps >= cfg.task_max_steps) local_stats[STAT_TIMEOUT] += 1;
-    else if (r - get_reward(cfg, s) == -1.0f) local_stats[STAT_SINGULAR] += 1;
+    if (!bad && cause == 2) local_stats[STAT_TIMEOUT] += 1;
+    else if (!bad && cause == 3) local_stats[STAT_SINGULAR] += 1;
+    else if (!bad && cause == 4) local_stats[STAT_DROP] += 1;
   }
   if (term_obs_row) for (int k = 0; k < JACO_NOBS; k++) term_obs_row[k] = obs[k];
   if (d && (auto_reset || bad)) { env_reset(cfg, s, env_id, obs); s.accum_rew = 0; }

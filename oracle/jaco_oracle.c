@@ -956,7 +956,7 @@ static real get_reward(jo_env *e) { /* util:312-446 */
     real d[3]; v3sub(d, e->gripper_pose, e->reach_goal);
     real dist = v3norm(d), ang = reach_ang_diff(e);
     real r = 5 * rexp(-dist) / 2 + 2 * rexp(-ang / (PI_ / 6)) / (2 * (dist * 15 + 1));
-    real w[3]; v3sub(w, e->ee_pos, e->base_pos);
+    real w[3]; v3sub(w, e->ee_pos, e->variant == JO_VAR_BASE ? e->base_pos : e->base_link_pos); /* cis:42,409 */
     real wb = v3norm(w);
     if (wb < R_(0.15)) r -= R_(0.15) - wb;
     if (e->gripper_pose[2] < R_(0.1)) r -= R_(0.1) - e->gripper_pose[2];
@@ -988,7 +988,7 @@ static real get_reward(jo_env *e) { /* util:312-446 */
 static int terminal_inspection(jo_env *e, real *bonus, real *wb, int *succ) {
   e->num_episodes += 1;
   real d[3]; *succ = 0; *bonus = 0;
-  v3sub(d, e->ee_pos, e->base_pos); *wb = v3norm(d);
+  v3sub(d, e->ee_pos, e->variant == JO_VAR_BASE ? e->base_pos : e->base_link_pos); *wb = v3norm(d); /* util:35,499; cis:42,590 */
   const real *op = e->obj_xpos;
   real dd[2] = {e->dest_goal[0] - op[0], e->dest_goal[1] - op[1]}, dest_diff = rsqrt_(dd[0] * dd[0] + dd[1] * dd[1]);
   real q2 = e->qpos[2];
@@ -1123,7 +1123,9 @@ void jo_step(jo_env *e, const double *action, float *obs, double *reward, int *d
   for (int i = 0; i < 7; i++) { double v = action[i]; if (v < -1) v = -1; if (v > 1) v = 1; a[i] = R_(v); }
   if (e->task == JO_TASK_REACHING) a[6] = 0;
   take_action(e, a);
-  if (e->task == JO_TASK_REACHING) { e->gripper_angle = R_(0.6); for (int i = 0; i < 50; i++) e->ramp[i] = R_(0.6); }
+  /* len(a) == 6 (util:625-626): gripper_angle = 0.6 for the observation, but gripper_angle_array is never refilled and
+   * stays np.zeros (util:37), so once action_in is set the finger servos are commanded 0.0 (util:76-79) */
+  if (e->task == JO_TASK_REACHING) { e->gripper_angle = R_(0.6); for (int i = 0; i < 50; i++) e->ramp[i] = 0; }
   for (int i = 0; i < 50; i++) { step_simulation(e); }
   get_observation(e, obs);
   real r = get_reward(e), bonus, w; int s, d;

@@ -213,3 +213,96 @@ def test_osc_pinv_branch_near_singularity():
                 continue
         assert np.allclose(u, u_ref, rtol=2e-3, atol=2e-2), (trial, u, u_ref)
     assert n_pinv >= 10
+
+
+# ------------------------------------------------------------------------------------------- production pipeline
+# The per-substep pipeline (mujoco_jaco_b200/csrc/jaco_pipe.cuh: K_S / K_B / K_S' / K_E) emulated sequentially on the
+# CPU by tests/harness with the launch order of jaco_kernel_pipe.cu.
+
+def test_pipeline_env_step_matches_oracle_picking():
+    n = 48
+    hs = HostSim(n, task="picking", seed=21)
+    hs.reset()
+    ora = _oracles("picking", 21, n)
+    for o in ora:
+        o.reset()
+    rng = np.random.default_rng(3)
+    dirty = 0
+    for step in range(4):
+        a = rng.uniform(-1, 1, (n, 7)).astype(np.float32)
+        obs, rew, done, succ, wb, info = hs.step_pipe(a)
+        dirty += int((info & 1).sum())
+        ref = [o.step(a[i].astype(np.float64)) for i, o in enumerate(ora)]
+        robs = np.stack([x[0] for x in ref]); rrew = np.array([x[1] for x in ref])
+        assert np.abs(obs - robs).max() < 1e-3
+        assert np.abs(rew - rrew).max() < 1e-5 * 5
+        assert np.array_equal(done.astype(bool), np.array([x[2] for x in ref]))
+        assert np.array_equal(succ, np.array([x[3] for x in ref]))
+        assert np.abs(wb - np.array([x[4] for x in ref])).max() < 1e-4
+        assert not (info & 2).any()                 # nothing handed back to the general path
+    assert dirty > 0                                # some envs did go through the dirty stream (K_B / K_S')
+
+
+def test_pipeline_matches_fused_hybrid_path():
+    """Same arithmetic, different schedule: the pipeline against the round-1 fused hybrid step on an ageing population."""
+    n = 64
+    a_, b_ = HostSim(n, task="picking", seed=0), HostSim(n, task="picking", seed=0)
+    a_.reset(); b_.reset()
+    rng = np.random.default_rng(0)
+    for step in range(12):
+        a = rng.uniform(-1, 1, (n, 7)).astype(np.float32)
+        o1, r1, d1, s1, w1, why = a_.step_fast(a, auto_reset=True, allow_fallback=2)
+        o2, r2, d2, s2, w2, info = b_.step_pipe(a, auto_reset=True)
+        assert np.abs(o1 - o2).max() < 2e-5 and np.abs(r1 - r2).max() < 1e-5
+        assert np.array_equal(d1, d2) and np.array_equal(s1, s2)
+    assert b_.stats[7] == 12 * n and b_.stats[11] > 0      # env steps counted, stage-B tasks served
+
+
+def test_pipeline_terminal_logic_and_in_kernel_reset():
+    hs = HostSim(4, task="picking", seed=2)
+    hs.reset()
+    q, v, aux = hs.get_state()
+    q[0, 11] = 0.05; q[0, 9:11] = [0.5, -0.5]          # env 0: object below z = 0.1 -> drop, -20
+    aux[1, 9] = 699                                     # env 1: time-out on this step
+    q[2, 2] = np.pi; aux[2, 46 + 2] = np.pi              # env 2: singular posture
+    hs.set_state(q, v, aux)
+    obs, rew, done, succ, wb, info = hs.step_pipe(np.zeros((4, 7), np.float32), auto_reset=True)
+    assert done[0] == 1 and rew[0] < -19
+    assert done[1] == 1 and -10.2 < rew[1] < -9.8 and wb[1] == 0
+    assert done[2] == 1 and -1.2 < rew[2] < -0.8
+    assert done[3] == 0 and succ.sum() == 0
+    assert hs.stats[0] == 3 and hs.stats[3] == 1 and hs.stats[4] == 1 and hs.stats[5] == 1   # episodes, time-out, drop, singular
+    # the three finished envs were re-initialised (in-kernel reset or general reset): identical to the oracle's reset
+    q2, v2, aux2 = hs.get_state()
+    for i in range(3):
+        o = OracleEnv(task="picking", seed=2, env_id=i)
+        qa, va, auxa = o.get_state()
+        qa[:], va[:] = q[i], v[i]
+        a64 = aux[i, :64].astype(np.float64)
+        o.set_state(qa, va, a64)
+        o.step(np.zeros(7))
+        oobs = o.reset()
+        assert np.abs(obs[i] - oobs).max() < 5e-6, i
+        oq, ov, oa = o.get_state()
+        assert np.abs(q2[i] - oq).max() < 1e-6 and np.abs(v2[i] - ov).max() < 1e-6
+        assert np.abs(aux2[i, :64] - oa).max() < 1e-5
+
+
+def test_reaching_sends_zero_finger_command_after_first_action():
+    """util:37,76-79,625-626: with a 6-D action gripper_angle_array is never refilled and stays zeros, so once action_in
+    is set the finger servos are commanded 0.0 (obs[7] keeps showing gripper_angle = 0.6).  Oracle, general path and
+    pipeline must agree on the finger joints after one step."""
+    n = 6
+    act = np.random.default_rng(4).uniform(-1, 1, (n, 6)).astype(np.float32)
+    hg = HostSim(n, task="reaching", seed=8); hg.reset()
+    hp = HostSim(n, task="reaching", seed=8); hp.reset()
+    ora = _oracles("reaching", 8, n)
+    for o in ora:
+        o.reset()
+    q0 = hg.get_state()[0][:, 6:9].copy()
+    og = hg.step(act); op = hp.step_pipe(act)
+    oq = np.stack([o.step(act[i].astype(np.float64)) and o.get_state()[0] for i, o in enumerate(ora)])
+    qg, qp = hg.get_state()[0], hp.get_state()[0]
+    assert np.abs(qg[:, 6:9] - oq[:, 6:9]).max() < 1e-5 and np.abs(qp[:, 6:9] - oq[:, 6:9]).max() < 1e-5
+    assert (oq[:, 6:9] < q0 - 1e-3).all()               # the fingers open towards 0, they do not hold 0.6
+    assert np.allclose(og[0][:, 7], -1.0) and np.allclose(op[0][:, 7], -1.0)   # (0.6 - 0.8) / 0.2
