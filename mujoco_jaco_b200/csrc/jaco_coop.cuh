@@ -89,6 +89,7 @@ struct CoopWS : CoopPub {
   // ---- results
   float qacc[JACO_NV], fcon[JACO_NV], touch[20];
   int iters;
+  int fingerobj;   // >= 1 contact between a hand-cluster geom (bodies 6..9) and the object (body 10): workload counter
   int solved;   // stage-B result (block mask) for the owner thread, which may sit in another warp (block task queue)
 };
 
@@ -698,6 +699,15 @@ JHD int coop_stageB(CoopWS& w) {
       else if (root != first) { comp[first] |= comp[root]; comp[root] = 0; rows[first] |= rows[root]; rows[root] = 0; }
     }
     if (first >= 0) rows[first] = 1;
+  }
+  COOP_LANE0 {
+    int fo = 0;
+    for (int c = 0; c < nc; c++) {
+      const JacoPair& P = MDLG.pairs[w.cpair[c]];
+      const int b1 = MDLG.geoms[P.g1].body, b2 = MDLG.geoms[P.g2].body;
+      if ((b1 == 10 && b2 >= 6 && b2 <= 9) || (b2 == 10 && b1 >= 6 && b1 <= 9)) fo = 1;
+    }
+    w.fingerobj = fo;
   }
   JPROF_T(c3);
   int solved = 0;

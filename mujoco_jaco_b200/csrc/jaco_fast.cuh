@@ -360,7 +360,7 @@ JHD int fast_osc(const ChainOut& c, const float* tq, const float* target, const 
     for (int i = 0; i < 6; i++) { d.ut[i] = ut[i]; d.u0[i] = u0[i]; for (int j = 0; j < 6; j++) d.J[i][j] = c.J[i][j]; }
     if (mode == OSC_DEFER) return 2;
     osc_finish_pinv(d, u);
-    return 1;
+    return 3;   // done, through the pinv branch (callers count it: STAT_PINV)
   }
   chol_solve_packed<6>(X, ut);  // ut <- Mx u_task
 #pragma unroll
@@ -1119,7 +1119,7 @@ JHD void scene_static(SceneBoxes& sb) {
   for (int i = 0; i < 9; i++) sb.hR[i] = G.R[i];
   v3copy(sb.oh, m.geoms[FG_OBJ].size); v3copy(sb.dh, m.geoms[FG_DEST].size);
 }
-// returns 0 when the first OSC torque needs the pinv branch and osc_mode == OSC_BAIL; 2 when deferred into *od
+// returns 0 when the first OSC torque needs the pinv branch and osc_mode == OSC_BAIL; 2 when deferred into *od; 3 = pinv ran inline
 JHD int step_begin(const JacoCfg& cfg, FastSim& s, const float* action, int osc_mode, OscDefer* od) {
   ChainOut c;
   {  // rebuild the controller-visible mjData at the lagged chain state
@@ -1198,7 +1198,7 @@ JHD void sub_forward(FastSim& s, SceneBoxes& sb, int it, SubFwd& f) {
   }
 }
 // solved: bit mask of the blocks (1 chain, 2 object, 4 dest) whose qacc_g / fcon_g come from the cooperative path.
-// Returns BAIL_* bits (0 = fine); osc_ret: result of the OSC for the next substep (1 done, 0 bail, 2 deferred into *od).
+// Returns BAIL_* bits (0 = fine); osc_ret: result of the OSC for the next substep (1 done, 3 done via pinv, 0 bail, 2 deferred into *od).
 template <bool COOP>
 JHD int sub_finish(FastSim& s, SubFwd& f, int it, int solved, const float* qacc_g, const float* fcon_g, int osc_mode, OscDefer* od, int* osc_ret) {
   const float h = MDL.dt;
@@ -1247,6 +1247,43 @@ JHD int step_end(const JacoCfg& cfg, FastSim& s, int env_id, float* obs, float* 
   return 1;
 }
 
+// ------------------------------------------------------------------------------------------- in-kernel reset
+// reset() of util:92-174 for the tasks whose reset needs no settle loop, without the general mj_forward: valid when no
+// arm geom can touch anything at the sampled pose (then every touch sensor reads 0, which is all the first observation
+// takes from that forward).  Returns 0 when the proximity tests cannot prove it: the caller hands the env to the
+// general reset kernel.
+JHD JNOINLINE int fast_reset(const JacoCfg& cfg, FastSim& s, int env_id, float* obs) {
+  if (cfg.task == JACO_TASK_PLACING || cfg.task == JACO_TASK_GRASPING) return 0;
+  reset_sample(cfg, s, env_id);
+  if (cfg.task != JACO_TASK_REACHING) {   // set_obj_xyz(obj_goal, [0,0,0,0]) (util:119-121, mujoco.py:217-227)
+    for (int i = 0; i < 3; i++) s.qpos[9 + i] = s.obj_goal[i];
+    for (int i = 0; i < 4; i++) s.qpos[12 + i] = 0;
+    for (int i = 9; i < JACO_NV; i++) s.qvel[i] = 0;
+  }
+  SceneBoxes sb; scene_static(sb);
+  FreeBody fo, fd;
+  free_body_setup(10, FG_OBJ, s.qpos + 9, s.qvel + 9, fo);    // also normalises the quaternions like mj_kinematics
+  free_body_setup(11, FG_DEST, s.qpos + 16, s.qvel + 15, fd);
+  v3copy(s.objp, fo.x);
+  v3copy(sb.op, fo.gp); v3copy(sb.dp, fd.gp);
+  for (int i = 0; i < 9; i++) { sb.oR[i] = fo.gR[i]; sb.dR[i] = fd.gR[i]; }
+  ChainOut c;
+  const float O0[3] = {0, 0, 0.5f};
+  fast_chain<true>(s.qpos, s.qvel, O0, &sb, c);
+  if (c.near) return 0;
+  for (int k = 0; k < 9; k++) if (MDL.ch_limited[k] && (s.qpos[k] - MDL.ch_range[k][0] < 0 || MDL.ch_range[k][1] - s.qpos[k] < 0)) return 0;
+  v3copy(s.eepos, c.eepos);
+  for (int i = 0; i < 4; i++) s.eeq[i] = c.eeq[i];
+  for (int i = 0; i < 9; i++) { s.lagq[i] = s.qpos[i]; s.lagv[i] = s.qvel[i]; }
+  s.touch_now = 0;
+  if (cfg.task == JACO_TASK_REACHING) { for (int i = 0; i < 6; i++) s.target[i] = s.reach_goal[i]; }
+  else { get_gripper_pose(s); for (int i = 0; i < 6; i++) s.target[i] = s.gripper_pose[i]; }
+  get_observation(cfg, s, env_id, obs);
+  s.rng_counter += 1;
+  s.accum_rew = 0;
+  return 1;
+}
+
 // One env step on the fast path, all 50 substeps in one call (CPU harness and diagnostics; the production kernels run
 // the same pieces substep by substep, jaco_pipe.cuh).  Returns FAST_OK with all outputs written into s / obs / ..., or
 // FAST_BAIL (reason bits in *why) with s in an unspecified state -- the caller must not store it.
@@ -1255,11 +1292,13 @@ JHD int step_end(const JacoCfg& cfg, FastSim& s, int env_id, float* obs, float* 
 // warp must then call this function together (lanes without an environment pass active = false).
 template <bool COOP>
 JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* action, float* obs, float* reward, int* done, int* succ, float* wb, int* why,
-                      CoopWS* ws = nullptr, bool active = true, int* cause = nullptr) {
+                      CoopWS* ws = nullptr, bool active = true, int* cause = nullptr, float* lst = nullptr) {
   *why = 0;
   int anyB = 0;
   int dead = 0;  // COOP: bail reason latched, the thread keeps pace with its warp until the step ends
-  if (!step_begin(cfg, s, action, COOP ? OSC_INLINE : OSC_BAIL, nullptr)) { *why = BAIL_OSC; if (!COOP) return FAST_BAIL; dead |= BAIL_OSC; }
+  { const int rb = step_begin(cfg, s, action, COOP ? OSC_INLINE : OSC_BAIL, nullptr);
+    if (!rb) { *why = BAIL_OSC; if (!COOP) return FAST_BAIL; dead |= BAIL_OSC; }
+    if (rb == 3 && lst && active) lst[STAT_PINV] += 1; }
   SceneBoxes sb;
   scene_static(sb);
   for (int it = 0; it < 50; it++) {
@@ -1311,6 +1350,12 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
           const CoopWS& wt = wsbase[slot - base];
           solved = wt.solved;
           if (solved) { for (int i = 0; i < JACO_NV; i++) { qacc_g[i] = wt.qacc[i]; fcon_g[i] = wt.fcon[i]; } if (it == 49) s.touch_now = touch_class(wt.touch); }
+          if (lst) {   // workload / cap counters (jaco_stats)
+            lst[STAT_STAGEB] += 1;
+            if (wt.ncon >= JACO_MAXCON) lst[STAT_CONCAP] += 1;
+            if (wt.iters >= JACO_SOLVER_MAXIT) lst[STAT_ITERCAP] += 1;
+            if (wt.fingerobj) lst[STAT_FINGEROBJ] += 1;
+          }
         }
         if (base + nwarps < ntask) __syncthreads();   // the next round's owners overwrite the workspaces
       }
@@ -1319,6 +1364,7 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
         FAST_WSTAT(2); anyB = 1;
         coop_publish(*ws, s, f.c, f.fo, f.fd, f.fsm, it == 49); coop_publish_contacts(*ws, ks, flags);
         solved = coop_stageB(*ws);
+        if (lst) { lst[STAT_STAGEB] += 1; if (ws->ncon >= JACO_MAXCON) lst[STAT_CONCAP] += 1; if (ws->iters >= JACO_SOLVER_MAXIT) lst[STAT_ITERCAP] += 1; if (ws->fingerobj) lst[STAT_FINGEROBJ] += 1; }
         if (solved) { FAST_WSTAT(3); FAST_WSTAT_ADD(4, ws->iters); FAST_WSTAT_ADD(5, ws->ncon); if (solved & 1) FAST_WSTAT(6); if (ws->ncon > 0) FAST_WSTAT(7);
           for (int i = 0; i < JACO_NV; i++) { qacc_g[i] = ws->qacc[i]; fcon_g[i] = ws->fcon[i]; } if (it == 49) s.touch_now = touch_class(ws->touch); }
       }
@@ -1328,6 +1374,7 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
     int osc_ret;
     const int dd = sub_finish<COOP>(s, f, it, solved, qacc_g, fcon_g, COOP ? OSC_INLINE : OSC_BAIL, nullptr, &osc_ret);
     if (dd) { *why = dd; if (!COOP) return FAST_BAIL; dead |= dd; }
+    if (osc_ret == 3 && lst && active && !dead) lst[STAT_PINV] += 1;
   }
   if (anyB) FAST_WSTAT(14);
   (void)anyB;
@@ -1401,7 +1448,7 @@ JHD int entry_step_fast(const JacoCfg& cfg, float* state, int N, int i, int env_
   float obs[JACO_NOBS], r, w; int d, sc;
   *needs_reset = 0;
   int cause = 0;
-  int rc = fast_env_step<COOP>(cfg, s, env_id, action_row, obs, &r, &d, &sc, &w, why, ws, active, &cause);
+  int rc = fast_env_step<COOP>(cfg, s, env_id, action_row, obs, &r, &d, &sc, &w, why, ws, active, &cause, local_stats);
   if (!active) return FAST_OK;
   if (rc != FAST_OK) return FAST_BAIL;
   s.accum_rew += r;
@@ -1411,10 +1458,15 @@ JHD int entry_step_fast(const JacoCfg& cfg, float* state, int N, int i, int env_
     if (cause == 2) local_stats[STAT_TIMEOUT] += 1;
     else if (cause == 3) local_stats[STAT_SINGULAR] += 1;
     else if (cause == 4) local_stats[STAT_DROP] += 1;
-    if (auto_reset) *needs_reset = 1;
+  }
+  if (term_obs_row) for (int k = 0; k < JACO_NOBS; k++) term_obs_row[k] = obs[k];
+  if (d && auto_reset) {
+    // reset() in place when the proximity tests prove the general mj_forward is not needed at the sampled pose
+    // (util:92-174); otherwise the caller queues the env for the general reset kernel
+    fast_store(state, N, i, s);
+    if (!fast_reset(cfg, s, env_id, obs)) { *needs_reset = 1; fast_load(state, N, i, s); }
   }
   fast_store(state, N, i, s);
-  if (term_obs_row) for (int k = 0; k < JACO_NOBS; k++) term_obs_row[k] = obs[k];
   for (int k = 0; k < JACO_NOBS; k++) obs_row[k] = obs[k];
   *reward = r; *done = (unsigned char)d; *succ = (unsigned char)sc; *wb = w;
   return FAST_OK;

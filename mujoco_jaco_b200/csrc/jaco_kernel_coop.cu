@@ -7,7 +7,7 @@
 __global__ void __launch_bounds__(JACO_FAST_BLOCK, JACO_FAST_MINBLOCKS) jaco_step_coop_kernel(const JacoStepArgs A) {
   const JacoCfg& cfg = A.cfg; float* state = A.state; const int N = A.N, env_offset = A.env_offset; const float* action = A.action;
   float* obs = A.obs; float* reward = A.reward; unsigned char* done = A.done; unsigned char* succ = A.succ; float* wb = A.wb;
-  float* term_obs = A.term_obs; const int auto_reset = A.auto_reset; float* gstats = A.gstats; int* worklist = A.worklist; int* counters = A.counters;
+  float* term_obs = A.term_obs; const int auto_reset = A.auto_reset; double* gstats = A.gstats; int* worklist = A.worklist; int* counters = A.counters;
 
   extern __shared__ __align__(16) unsigned char coop_smem[];
   CoopWS* ws = reinterpret_cast<CoopWS*>(coop_smem) + (threadIdx.x >> 5);

@@ -4,7 +4,7 @@
 __global__ void __launch_bounds__(JACO_FAST_BLOCK, JACO_FAST_MINBLOCKS) jaco_step_fast_kernel(const JacoStepArgs A) {
   const JacoCfg& cfg = A.cfg; float* state = A.state; const int N = A.N, env_offset = A.env_offset; const float* action = A.action;
   float* obs = A.obs; float* reward = A.reward; unsigned char* done = A.done; unsigned char* succ = A.succ; float* wb = A.wb;
-  float* term_obs = A.term_obs; const int auto_reset = A.auto_reset; float* gstats = A.gstats; int* worklist = A.worklist; int* counters = A.counters;
+  float* term_obs = A.term_obs; const int auto_reset = A.auto_reset; double* gstats = A.gstats; int* worklist = A.worklist; int* counters = A.counters;
 
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   float local[16];

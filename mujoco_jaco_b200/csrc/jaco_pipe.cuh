@@ -58,43 +58,6 @@ struct PipeBufs {
 #define PIPE_STAT(gs, k) ((gs)[k] += 1.0)
 #endif
 
-// ------------------------------------------------------------------------------------------- in-kernel reset
-// reset() of util:92-174 for the tasks whose reset needs no settle loop, without the general mj_forward: valid when no
-// arm geom can touch anything at the sampled pose (then every touch sensor reads 0, which is all the first observation
-// takes from that forward).  Returns 0 when the proximity tests cannot prove it: the caller hands the env to the
-// general reset kernel.
-JHD int fast_reset(const JacoCfg& cfg, FastSim& s, int env_id, float* obs) {
-  if (cfg.task == JACO_TASK_PLACING || cfg.task == JACO_TASK_GRASPING) return 0;
-  reset_sample(cfg, s, env_id);
-  if (cfg.task != JACO_TASK_REACHING) {   // set_obj_xyz(obj_goal, [0,0,0,0]) (util:119-121, mujoco.py:217-227)
-    for (int i = 0; i < 3; i++) s.qpos[9 + i] = s.obj_goal[i];
-    for (int i = 0; i < 4; i++) s.qpos[12 + i] = 0;
-    for (int i = 9; i < JACO_NV; i++) s.qvel[i] = 0;
-  }
-  SceneBoxes sb; scene_static(sb);
-  FreeBody fo, fd;
-  free_body_setup(10, FG_OBJ, s.qpos + 9, s.qvel + 9, fo);    // also normalises the quaternions like mj_kinematics
-  free_body_setup(11, FG_DEST, s.qpos + 16, s.qvel + 15, fd);
-  v3copy(s.objp, fo.x);
-  v3copy(sb.op, fo.gp); v3copy(sb.dp, fd.gp);
-  for (int i = 0; i < 9; i++) { sb.oR[i] = fo.gR[i]; sb.dR[i] = fd.gR[i]; }
-  ChainOut c;
-  const float O0[3] = {0, 0, 0.5f};
-  fast_chain<true>(s.qpos, s.qvel, O0, &sb, c);
-  if (c.near) return 0;
-  for (int k = 0; k < 9; k++) if (MDL.ch_limited[k] && (s.qpos[k] - MDL.ch_range[k][0] < 0 || MDL.ch_range[k][1] - s.qpos[k] < 0)) return 0;
-  v3copy(s.eepos, c.eepos);
-  for (int i = 0; i < 4; i++) s.eeq[i] = c.eeq[i];
-  for (int i = 0; i < 9; i++) { s.lagq[i] = s.qpos[i]; s.lagv[i] = s.qvel[i]; }
-  s.touch_now = 0;
-  if (cfg.task == JACO_TASK_REACHING) { for (int i = 0; i < 6; i++) s.target[i] = s.reach_goal[i]; }
-  else { get_gripper_pose(s); for (int i = 0; i < 6; i++) s.target[i] = s.gripper_pose[i]; }
-  get_observation(cfg, s, env_id, obs);
-  s.rng_counter += 1;
-  s.accum_rew = 0;
-  return 1;
-}
-
 // ------------------------------------------------------------------------------------------- K_S: one substep
 // Substep B.it[i] of env i (the env step is begun first when it has not been).  Returns 1 when the env now has a pending
 // task for the dirty stream (general contact pass or deferred pinv), else 0.  dirty_stream: the call comes from K_S'
@@ -279,9 +242,7 @@ JHD void pipe_task(const JacoCfg& cfg, const PipeBufs& B, int i, CoopWS& w, doub
       if (it == 49 && (sv & 1)) PSC(SC_TOUCH) = (float)touch_class(w.touch);
       if (w.ncon >= JACO_MAXCON) PIPE_STAT(gstats, STAT_CONCAP);
       if (w.iters >= JACO_SOLVER_MAXIT) PIPE_STAT(gstats, STAT_ITERCAP);
-      { int fo = 0; for (int c = 0; c < w.ncon; c++) { const JacoPair& P = MDLG.pairs[w.cpair[c]]; const int b1 = MDLG.geoms[P.g1].body, b2 = MDLG.geoms[P.g2].body;
-          if ((b1 == 10 && b2 >= 6 && b2 <= 9) || (b2 == 10 && b1 >= 6 && b1 <= 9)) fo = 1; }
-        if (fo) PIPE_STAT(gstats, STAT_FINGEROBJ); }
+      if (w.fingerobj) PIPE_STAT(gstats, STAT_FINGEROBJ);
       pipe_tail_chain(cfg, B, i, r, w, sv, it, gstats);
       B.pend[i] = PEND_NONE;
     }
