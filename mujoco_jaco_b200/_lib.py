@@ -10,8 +10,8 @@ REPO = os.path.dirname(HERE)
 SO_PATH = os.path.join(HERE, "libjaco_b200.so")
 CSRC = os.path.join(HERE, "csrc")
 UNITS = ["jaco_kernels.cu", "jaco_kernel_coop.cu"]            # compiled in parallel, linked into one .so
-DIAG_UNITS = ["jaco_kernel_fast.cu", "jaco_kernel_pipe.cu"]   # A/B variants: only in -DJACO_DIAG builds (scripts/build_variant.sh)
-HEADERS = [os.path.join(CSRC, f) for f in ("jaco_sim.cuh", "jaco_fast.cuh", "jaco_coop.cuh", "jaco_pipe.cuh", "jaco_launch.h", "jaco_model.h")] + [
+DIAG_UNITS = []
+HEADERS = [os.path.join(CSRC, f) for f in ("jaco_sim.cuh", "jaco_fast.cuh", "jaco_coop.cuh", "jaco_launch.h", "jaco_model.h")] + [
     os.path.join(REPO, "include", "jaco_b200.h"), os.path.join(REPO, "include", "jaco_model_layout.h")]
 SOURCES = [os.path.join(CSRC, u) for u in UNITS] + HEADERS
 # -prec-div=false -prec-sqrt=false -ftz=true: 2-ulp division / square root and flushed denormals.  IEEE division and

@@ -58,9 +58,7 @@ struct CoopSink {  // contacts of one geom pair (<= 8: box-box clipping cap)
   float cpos[8][3], cn[8][3], cdist[8];
 };
 
-// What the owner thread publishes: the mj_forward quantities of this substep the cooperative path consumes.  Kept as the
-// leading base sub-object of CoopWS so that the pipeline (jaco_pipe.cuh) can stage it through a global-memory record
-// and copy it word by word into a warp's shared-memory workspace.
+// What the owner thread publishes: the mj_forward quantities of this substep the cooperative path consumes.
 struct CoopPub {
   float bx[JACO_NBODY][3], bR[JACO_NBODY][9], ax[9][3], bw[JACO_NBODY][3], bv[JACO_NBODY][3];
   float qpos9[9], qvel[JACO_NV], Mc[45], Mf[2][21], asm_[JACO_NV], warm[JACO_NV];

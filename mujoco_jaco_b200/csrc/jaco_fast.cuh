@@ -766,6 +766,10 @@ JHD void fast_solve6(Rows4& r, const FreeBody& fb, const float* as_, const float
 // forward + Euler of one free box whose contacts (if any) are in `c`: updates q7 / v6 / warm6
 JHD void fast_free_step(FreeBody& fb, const Con4& c, float* q7, float* v6, float* warm6) {
   const float h = MDL.dt;
+#if defined(JACO_COLLISION_STATS) && !defined(__CUDACC__)
+  float in_[19]; for (int i = 0; i < 7; i++) in_[i] = q7[i]; for (int i = 0; i < 6; i++) { in_[7 + i] = v6[i]; in_[13 + i] = warm6[i]; }
+  struct Probe { float* q; float* v; float* w; float* in; ~Probe() { int same = 1; for (int i = 0; i < 7; i++) same &= (q[i] == in[i]); for (int i = 0; i < 6; i++) same &= (v[i] == in[7 + i]) && (w[i] == in[13 + i]); FAST_WSTAT(11); if (same) FAST_WSTAT(12); } } probe_{q7, v6, warm6, in_};
+#endif
   float fsm[6], as_[6], a[6], fcon[6];
 #pragma unroll
   for (int i = 0; i < 6; i++) { fsm[i] = -fb.bias[i]; as_[i] = fsm[i]; }
@@ -900,6 +904,12 @@ JHD void coop_publish(CoopPub& w, const FastSim& s, const ChainOut& c, const Fre
 #define JSYNC1()
 #define JSYNC2()
 #define JSYNC3()
+#endif
+#ifndef JACO_NOCOOP_OSC_MODE
+#define JACO_NOCOOP_OSC_MODE OSC_INLINE   // bail-only fast path (pass 1 of the env step): the OSC's pinv branch runs in place, it is not a reason to bail
+#endif
+#ifndef JACO_COOP_NWS
+#define JACO_COOP_NWS 8   // cooperative workspaces (= serving warps) per block of the fused kernel: 8 x 22 KB of dynamic shared memory
 #endif
 #ifndef JACO_TIMING_SKIP   /* timing experiments only (scripts/build_variant.sh): bit 0 no stage B, bit 1 no arm collision, bit 2 arm stage A only */
 #define JACO_TIMING_SKIP 0
@@ -1101,8 +1111,7 @@ JHD void free_integrate(const FreeBody& fb, const float* a6, const float* fcon6,
 }
 
 // ------------------------------------------------------------------------------------------- step pieces
-// The env step is cut into pieces that the legacy one-kernel path (fast_env_step below: CPU harness, diagnostics) and the
-// per-substep pipeline (jaco_pipe.cuh: the production kernels) share:
+// The env step in pieces (fast_env_step below strings them together):
 //   step_begin    lagged controller data, _take_action, first OSC torque
 //   sub_forward   mj_forward of the fast regime at the current state: limits, free boxes, scene contacts, chain pass
 //   sub_finish    mj_Euler for the three blocks (with the cooperative path's qacc / fcon where it solved a block),
@@ -1284,8 +1293,7 @@ JHD JNOINLINE int fast_reset(const JacoCfg& cfg, FastSim& s, int env_id, float* 
   return 1;
 }
 
-// One env step on the fast path, all 50 substeps in one call (CPU harness and diagnostics; the production kernels run
-// the same pieces substep by substep, jaco_pipe.cuh).  Returns FAST_OK with all outputs written into s / obs / ..., or
+// One env step on the fast path, all 50 substeps in one call.  Returns FAST_OK with all outputs written into s / obs / ..., or
 // FAST_BAIL (reason bits in *why) with s in an unspecified state -- the caller must not store it.
 // COOP = true: nothing bails for contact reasons; environments that need the general contact handling get it from
 // the warp-cooperative path (jaco_coop.cuh) through the per-warp workspace ws, substep by substep.  All lanes of a
@@ -1296,7 +1304,7 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
   *why = 0;
   int anyB = 0;
   int dead = 0;  // COOP: bail reason latched, the thread keeps pace with its warp until the step ends
-  { const int rb = step_begin(cfg, s, action, COOP ? OSC_INLINE : OSC_BAIL, nullptr);
+  { const int rb = step_begin(cfg, s, action, COOP ? OSC_INLINE : JACO_NOCOOP_OSC_MODE, nullptr);
     if (!rb) { *why = BAIL_OSC; if (!COOP) return FAST_BAIL; dead |= BAIL_OSC; }
     if (rb == 3 && lst && active) lst[STAT_PINV] += 1; }
   SceneBoxes sb;
@@ -1306,7 +1314,13 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
     SubFwd f;
     sub_forward<COOP>(s, sb, it, f);
     const int bail = f.bail;
-    if (!COOP && bail) { *why = bail; return FAST_BAIL; }
+    if (!COOP && bail) {
+      // pass 1: "near" is only a bounding-sphere statement.  Run the owner-thread narrow phase over the arm pairs and leave the
+      // fast path only when there is something to solve (an arm contact, an active limit, non-simple scene contacts).
+      bool leave = (bail & (BAIL_LIMIT | BAIL_OBJ | BAIL_DEST)) != 0;
+      if (!leave) { LocalSink ks; ks.ncon = 0; fast_arm_collide(f.c, f.fo, f.fd, ks); leave = ks.ncon > 0; }
+      if (leave) { *why = bail; return FAST_BAIL; }
+    }
     // ---- general contact handling on demand (warp-cooperative)
     int solved = 0;   // bit mask of the blocks (1 chain, 2 object, 4 dest) the cooperative path solved for this env
     float qacc_g[JACO_NV], fcon_g[JACO_NV];
@@ -1325,7 +1339,8 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
       // warp that happens to own the most.  Owners publish into the workspace of the serving warp (all owners of a
       // round at the same time) and read their results back from it.
       __shared__ int q_n;
-      const int nwarps = blockDim.x >> 5, mywarp = threadIdx.x >> 5;
+      const int mywarp = threadIdx.x >> 5;
+      const int nwarps = min((int)(blockDim.x >> 5), JACO_COOP_NWS);   // serving warps = workspaces of the block
       CoopWS* const wsbase = ws - mywarp;
       if (threadIdx.x == 0) q_n = 0;
       __syncthreads();
@@ -1339,7 +1354,7 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
         if (mine) { CoopWS& wt = wsbase[slot - base]; coop_publish(wt, s, f.c, f.fo, f.fd, f.fsm, it == 49); coop_publish_contacts(wt, ks, flags); }
         __syncthreads();
         JPROF_T(t2);
-        if (base + mywarp < ntask) {
+        if (mywarp < nwarps && base + mywarp < ntask) {
           const int sv = coop_stageB(*ws);
           if ((threadIdx.x & 31) == 0) ws->solved = sv;
           JPROF_T(t3);
@@ -1372,7 +1387,7 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
     }
     JSYNC2();
     int osc_ret;
-    const int dd = sub_finish<COOP>(s, f, it, solved, qacc_g, fcon_g, COOP ? OSC_INLINE : OSC_BAIL, nullptr, &osc_ret);
+    const int dd = sub_finish<COOP>(s, f, it, solved, qacc_g, fcon_g, COOP ? OSC_INLINE : JACO_NOCOOP_OSC_MODE, nullptr, &osc_ret);
     if (dd) { *why = dd; if (!COOP) return FAST_BAIL; dead |= dd; }
     if (osc_ret == 3 && lst && active && !dead) lst[STAT_PINV] += 1;
   }
@@ -1465,6 +1480,13 @@ JHD int entry_step_fast(const JacoCfg& cfg, float* state, int N, int i, int env_
     // (util:92-174); otherwise the caller queues the env for the general reset kernel
     fast_store(state, N, i, s);
     if (!fast_reset(cfg, s, env_id, obs)) { *needs_reset = 1; fast_load(state, N, i, s); }
+    else {   // the new episode's goals (rows fast_store leaves alone: they are constant within an episode)
+      const int A = JACO_NQ + JACO_NV;
+#pragma unroll
+      for (int k = 0; k < 3; k++) { state[(size_t)(A + AUX_OBJ_GOAL + k) * N + i] = s.obj_goal[k]; state[(size_t)(A + AUX_DEST_GOAL + k) * N + i] = s.dest_goal[k]; }
+#pragma unroll
+      for (int k = 0; k < 6; k++) state[(size_t)(A + AUX_REACH_GOAL + k) * N + i] = s.reach_goal[k];
+    }
   }
   fast_store(state, N, i, s);
   for (int k = 0; k < JACO_NOBS; k++) obs_row[k] = obs[k];

@@ -1,6 +1,12 @@
 // jaco_kernel_coop.cu -- the production step kernel: fast path per thread + warp-cooperative general contact
-// handling on demand (jaco_fast.cuh, jaco_coop.cuh).
+// handling on demand (jaco_fast.cuh, jaco_coop.cuh), all 50 substeps of one env step in one launch.
+//
+// Alternatives measured and rejected this round (profiles/r02_*): a per-substep kernel pipeline with the rare
+// paths on a second stream (90-114 ms per 65 536-env step against 44), and a two-pass split (bail-only fast kernel, then
+// this kernel over the dirty list: 84-98 ms) -- the general contact pass is throughput-bound on instruction delivery and
+// needs every SM's warps, which this single kernel gives it substep by substep.
 #include "jaco_launch.h"
+#define JACO_COOP_WSN ((JACO_FAST_BLOCK / 32) < JACO_COOP_NWS ? (JACO_FAST_BLOCK / 32) : JACO_COOP_NWS)
 
 // hybrid kernel: fast path per thread + warp-cooperative general contact handling on demand (jaco_coop.cuh);
 // one CoopWS per warp in dynamic shared memory
@@ -40,11 +46,11 @@ __global__ void __launch_bounds__(JACO_FAST_BLOCK, JACO_FAST_MINBLOCKS) jaco_ste
 cudaError_t jaco_coop_upload_model(const JacoModel* m) {
   cudaError_t e = cudaMemcpyToSymbol(c_jaco_model, m, sizeof(JacoModel));
   if (e == cudaSuccess) e = cudaMemcpyToSymbol(g_jaco_model_dev, m, sizeof(JacoModel));
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(jaco_step_coop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(CoopWS) * (JACO_FAST_BLOCK / 32)));
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(jaco_step_coop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(CoopWS) * JACO_COOP_WSN));
   return e;
 }
 cudaError_t jaco_coop_launch(const JacoStepArgs& a, cudaStream_t st) {
-  const size_t smem = sizeof(CoopWS) * (JACO_FAST_BLOCK / 32);
+  const size_t smem = sizeof(CoopWS) * JACO_COOP_WSN;
   jaco_step_coop_kernel<<<(a.N + JACO_FAST_BLOCK - 1) / JACO_FAST_BLOCK, JACO_FAST_BLOCK, smem, st>>>(a);
   return cudaGetLastError();
 }

@@ -1,7 +1,7 @@
 // jaco_kernels.cu -- the C ABI of libjaco_b200.so (include/jaco_b200.h) and the general-path kernels.
 // The production env step is the fused hybrid kernel of jaco_kernel_coop.cu; the kernels here are the general
 // thread-per-env path (reset, raw mj_step for parity injection, and the work-list kernel that re-runs the few envs the
-// pipeline hands back).  State is SoA in HBM so every load/store of a warp is one coalesced 128-byte line per state
+// step kernel hands back).  State is SoA in HBM so every load/store of a warp is one coalesced 128-byte line per state
 // row; model constants sit in __constant__ memory (uniform broadcast reads).  See DESIGN.md.
 #include <cuda_runtime.h>
 #include <stdio.h>
@@ -14,15 +14,14 @@
 #define JACO_BLOCK 128
 
 struct jaco_sim_handle {
-  int n, device, env_offset;
+  int n, device, env_offset, sms;
   JacoCfg cfg;
   float* state;       // [JACO_NSTATE][n]
   double* stats;      // [16] (double on the device: a float counter stops counting at 2^24)
   float *s_action, *s_obs, *s_reward, *s_wb; unsigned char *s_done, *s_succ;  // staging for jaco_step_host
-  int use_fast;        // 2 fused hybrid kernel (production), 0 general kernel; diagnostic builds: 3 per-substep pipeline, 1 bail-only fast kernel
-  int* worklist;       // [2][n] env indices: row 0 = handed back by the pipeline, row 1 = finished episodes to reset
-  int* counters;       // [16]: 0 n_bail, 1 n_reset, 2.. bail-reason histogram (cumulative, diagnostics)
-  JacoPipe pipe;
+  int use_fast;        // 2 fused hybrid kernel (production), 0 general kernel
+  int* worklist;       // [2][n] env indices: row 0 = general-path fall-backs, row 1 = finished episodes that need the general reset
+  int* counters;       // [16]: 0 n_fallback, 1 n_reset, 2..7 bail-reason histogram (cumulative, diagnostics)
   JacoModel* model;    // host copy: the model symbols are per library, a handle re-uploads them when another handle used them last
   long long launches;
   char err[256];
@@ -137,10 +136,6 @@ static cudaError_t upload_model(jaco_sim_handle* h) {
   cudaError_t e = cudaMemcpyToSymbol(c_jaco_model, h->model, sizeof(JacoModel));
   if (e == cudaSuccess) e = cudaMemcpyToSymbol(g_jaco_model_dev, h->model, sizeof(JacoModel));
   if (e == cudaSuccess) e = jaco_coop_upload_model(h->model);
-#ifdef JACO_DIAG
-  if (e == cudaSuccess) e = jaco_fast_upload_model(h->model);
-  if (e == cudaSuccess) e = jaco_pipe_upload_model(h->model);
-#endif
   if (e == cudaSuccess) g_model_owner = h;
   return e;
 }
@@ -163,21 +158,17 @@ int jaco_create(const void* model_blob, size_t nbytes, int n_envs, int task_id, 
   CK(cudaMalloc(&h->state, sizeof(float) * JACO_NSTATE * (size_t)n_envs));
   CK(cudaMemset(h->state, 0, sizeof(float) * JACO_NSTATE * (size_t)n_envs));
   h->use_fast = fast_model_ok(*h->model) ? 2 : 0;        /* production: the fused hybrid kernel; a model without the hard-wired scene structure runs the general kernel */
-#ifdef JACO_DIAG   /* diagnostic builds only: the per-substep pipeline and the bail-only fast kernel for A/B timing and cross-checks */
-  if (getenv("JACO_PIPE") && h->use_fast) h->use_fast = 3;
-  if (getenv("JACO_NO_COOP") && h->use_fast) h->use_fast = 1;
+#ifdef JACO_DIAG   /* diagnostic builds only: the general thread-per-env kernel for cross-checks */
   if (getenv("JACO_NO_FAST")) h->use_fast = 0;
 #endif
   CK(cudaMalloc(&h->worklist, sizeof(int) * 2 * (size_t)n_envs));
+  h->sms = 148; cudaDeviceGetAttribute(&h->sms, cudaDevAttrMultiProcessorCount, device);
   CK(cudaMalloc(&h->counters, sizeof(int) * 16));
   CK(cudaMemset(h->counters, 0, sizeof(int) * 16));
   CK(cudaMalloc(&h->stats, sizeof(double) * JACO_NSTATS));
   CK(cudaMemset(h->stats, 0, sizeof(double) * JACO_NSTATS));
   CK(cudaFuncSetAttribute(jaco_step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 0));
   CK(cudaFuncSetAttribute(jaco_reset_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 0));
-#ifdef JACO_DIAG
-  CK(jaco_pipe_create(&h->pipe, n_envs, device));
-#endif
   return JACO_OK;
 }
 
@@ -185,9 +176,6 @@ void jaco_destroy(jaco_handle h) {
   if (!h) return;
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
-#ifdef JACO_DIAG
-  jaco_pipe_destroy(&h->pipe);
-#endif
   cudaFree(h->state); cudaFree(h->stats); cudaFree(h->worklist); cudaFree(h->counters);
   cudaFree(h->s_action); cudaFree(h->s_obs); cudaFree(h->s_reward); cudaFree(h->s_wb); cudaFree(h->s_done); cudaFree(h->s_succ);
   if (g_model_owner == h) g_model_owner = nullptr;
@@ -201,7 +189,7 @@ int jaco_debug_counters(jaco_handle h, int* out16) {  /* host copy of the work-l
   return JACO_OK;
 }
 int jaco_n_envs(jaco_handle h) { return h ? h->n : 0; }
-long long jaco_launch_count(jaco_handle h) { return h ? h->launches + h->pipe.launches : 0; }
+long long jaco_launch_count(jaco_handle h) { return h ? h->launches : 0; }
 
 static inline int nblocks(int n) { return (n + JACO_BLOCK - 1) / JACO_BLOCK; }
 
@@ -226,20 +214,6 @@ int jaco_step(jaco_handle h, const float* action, float* obs, float* reward, uin
     jaco_step_list_kernel<<<nlist, JACO_LIST_BLOCK, 0, st>>>(h->cfg, h->state, nullptr, h->n, h->env_offset, action, obs, reward, done, succ, wb,
                                                            term_obs, auto_reset, h->stats, h->worklist, h->counters);
     h->launches += 2;
-#ifdef JACO_DIAG
-  } else if (h->use_fast == 3) {
-    CK(cudaMemsetAsync(h->counters, 0, 2 * sizeof(int), st));
-    CK(jaco_pipe_step(&h->pipe, A, h->stats, st));
-    jaco_step_list_kernel<<<nlist, JACO_LIST_BLOCK, 0, st>>>(h->cfg, h->state, h->pipe.state_prev, h->n, h->env_offset, action, obs, reward, done, succ, wb,
-                                                           term_obs, auto_reset, h->stats, h->worklist, h->counters);
-    h->launches += 1;
-  } else if (h->use_fast == 1) {
-    CK(cudaMemsetAsync(h->counters, 0, 2 * sizeof(int), st));
-    CK(jaco_fast_launch(A, st));
-    jaco_step_list_kernel<<<nlist, JACO_LIST_BLOCK, 0, st>>>(h->cfg, h->state, nullptr, h->n, h->env_offset, action, obs, reward, done, succ, wb,
-                                                           term_obs, auto_reset, h->stats, h->worklist, h->counters);
-    h->launches += 2;
-#endif
   } else {
     jaco_step_kernel<<<nblocks(h->n), JACO_BLOCK, 0, st>>>(h->cfg, h->state, h->n, h->env_offset, action, obs, reward, done, succ, wb, term_obs, auto_reset, h->stats);
     h->launches++;

@@ -726,6 +726,10 @@ JHD float impedance(const float* solimp, float x) {  // getimpedance, x = pos - 
   if (xx == 0) return d0;
   float y;
   if (power == 1) y = xx;
+  else if (power == 2) {   // MuJoCo's default exponent: a plain square instead of powf (same value to the last bits that matter, ~60 fewer instructions per row)
+    if (xx <= mid) { const float a = xx / mid; y = a * a * mid; }
+    else { const float a = (1 - xx) / (1 - mid); y = 1 - a * a * (1 - mid); }
+  }
   else if (xx <= mid) y = powf(xx / mid, power) * mid;
   else y = 1 - powf((1 - xx) / (1 - mid), power) * (1 - mid);
   return d0 + y * (dw - d0);
@@ -1518,7 +1522,7 @@ JHD float round_half(float v) {  // value after a round trip through np.float16 
   return ldexpf(mnt, ex);
 }
 // sim.reset() + _create_init_angle + __sample_goal + set_dest_xyz (util:92-103,176-221; mujoco.py:229-237): everything of
-// reset() that precedes the first mj_forward.  Shared by the general reset (env_reset) and the pipeline's in-kernel reset
+// reset() that precedes the first mj_forward.  Shared by the general reset (env_reset) and the in-place reset of the fast path
 // (jaco_fast.cuh fast_reset); S = JacoSim or FastSim.
 template <class S>
 JHD void reset_sample(const JacoCfg& cfg, S& s, int env_id) {
@@ -1670,7 +1674,7 @@ JHD void refresh_lagged(JacoSim& s) {
   for (int k = 0; k < 9; k++) { s.qpos[k] = q[k]; s.qvel[k] = v[k]; }
 }
 
-// episode / workload counters (jaco_stats): 0-8 episode statistics, 9-15 workload and cap counters of the step pipeline
+// episode / workload counters (jaco_stats): 0-8 episode statistics, 9-15 workload and cap counters of the step kernels
 enum { STAT_EPISODES = 0, STAT_SUCCESS = 1, STAT_RETURN = 2, STAT_TIMEOUT = 3, STAT_DROP = 4, STAT_SINGULAR = 5, STAT_NAN = 6, STAT_STEPS = 7, STAT_LENGTH = 8,
        STAT_CONCAP = 9,      // env-substeps whose contact list hit JACO_MAXCON / the row pool (contacts were dropped)
        STAT_ITERCAP = 10,    // Newton solves that stopped on the iteration cap instead of the convergence test

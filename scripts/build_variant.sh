@@ -6,6 +6,5 @@ cd "$(dirname "$0")/../mujoco_jaco_b200"
 tag=$1; shift
 mkdir -p build_var_$tag
 /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -prec-div=false -prec-sqrt=false -ftz=true -Xcompiler -fPIC "$@" -c -o build_var_$tag/jaco_kernel_coop.o csrc/jaco_kernel_coop.cu
-while [ ! -f build/jaco_kernels.o ] || [ build/jaco_kernels.o -ot csrc/jaco_fast.cuh ] || [ build/jaco_kernel_fast.o -ot csrc/jaco_fast.cuh ]; do sleep 5; done
-/usr/local/cuda/bin/nvcc -shared -o libjaco_b200_$tag.so build/jaco_kernels.o build/jaco_kernel_fast.o build_var_$tag/jaco_kernel_coop.o
+/usr/local/cuda/bin/nvcc -shared -o libjaco_b200_$tag.so build/jaco_kernels.o build_var_$tag/jaco_kernel_coop.o
 echo built $tag

@@ -4,7 +4,7 @@
 #include <string.h>
 #define JACO_COLLISION_STATS 1
 #include <vector>
-#include "../../mujoco_jaco_b200/csrc/jaco_pipe.cuh"
+#include "../../mujoco_jaco_b200/csrc/jaco_fast.cuh"
 
 extern "C" {
 void hh_init(const double* blob) { jaco_model_from_blob(blob, &g_jaco_model_host); }
@@ -94,41 +94,19 @@ extern "C" void hh_body_spheres(float* out16) { memcpy(out16, g_jaco_model_host.
 extern "C" void hh_scale_spheres(float f) { for (int b = 0; b < 4; b++) g_jaco_model_host.body_sphere[b][3] *= f; }
 extern "C" int hh_sizeof_coopws() { return (int)sizeof(CoopWS); }
 
-// The production pipeline (jaco_pipe.cuh) run sequentially on the CPU with the launch order of jaco_kernel_pipe.cu:
-// K_S(k) over the clean envs, then dirty iteration k = K_B over the pending tasks + K_S' over the dirty envs, K_E at the
-// end; envs the pipeline gives up on are re-run by the general path from the pre-step state, like on the device.
-// info[i]: bit 0 env went dirty, bit 1 general-path fallback, bit 2 general reset.
-extern "C" void hh_step_pipe(int task, int variant, unsigned long long seed, int env_offset, float* state, int N, const float* action, float* obs,
+// The production env step (jaco_kernel_coop.cu) with the device's protocol: the hybrid path (fast path + cooperative general
+// contact handling) for every env; the general path for what it hands back (NaN guard / bad pivot); the general reset where
+// the in-place reset declined.  info[i]: bit 0 the cooperative path served the env, bit 1 general-path fall-back, bit 2 general reset.
+extern "C" void hh_step_hybrid(int task, int variant, unsigned long long seed, int env_offset, float* state, int N, const float* action, float* obs,
              float* reward, unsigned char* done, unsigned char* succ, float* wb, int auto_reset, float* stats16, int* info) {
   JacoCfg c = mkcfg(task, variant, seed);
-  std::vector<float> scratch((size_t)PIPE_NSCR * N, 0.0f), prev(state, state + (size_t)JACO_NSTATE * N);
-  std::vector<PipeRec> rec(N);
-  std::vector<int> it(N, -1), pend(N, 0), dirty(N, 0), dead(N, 0), dlist(N, 0);
-  PipeBufs B = {state, scratch.data(), rec.data(), it.data(), pend.data(), dirty.data(), dead.data(), N};
-  double gstats[16] = {0};
   static CoopWS ws;
-  int ndirty = 0;
-  for (int k = 0; k <= 50; k++) {   // dirty iteration 50 only serves tasks published by K_S' of iteration 49
-    if (k < 50) for (int i = 0; i < N; i++) if (!dirty[i]) { if (pipe_env_substep(c, B, i, action + (size_t)i * 7, false, gstats)) { dirty[i] = 1; dlist[ndirty++] = i; } }
-    const int snap = ndirty;
-    for (int t = 0; t < snap; t++) pipe_task(c, B, dlist[t], ws, gstats);
-    if (k < 50) for (int t = 0; t < snap; t++) { const int i = dlist[t]; if (pend[i] == PEND_NONE && it[i] < 50) pipe_env_substep(c, B, i, action + (size_t)i * 7, true, gstats); }
-  }
-  float local[16] = {0};
   for (int i = 0; i < N; i++) {
-    if (info) info[i] = dirty[i] ? 1 : 0;
-    const int rc = pipe_env_end(c, B, i, env_offset + i, obs + (size_t)i * JACO_NOBS, reward + i, done + i, succ + i, wb + i, nullptr, auto_reset, local);
-    if (rc == 1) {
-      for (int r = 0; r < JACO_NSTATE; r++) state[(size_t)r * N + i] = prev[(size_t)r * N + i];
-      entry_step(c, state, N, i, env_offset + i, action + (size_t)i * 7, obs + (size_t)i * JACO_NOBS, reward + i, done + i, succ + i, wb + i, 0, auto_reset, local);
-      local[STAT_FALLBACK] += 1;
-      if (info) info[i] |= 2;
-    } else if (rc == 2) {
-      entry_reset(c, state, N, i, env_offset + i, obs + (size_t)i * JACO_NOBS);
-      local[STAT_GENRESET] += 1;
-      if (info) info[i] |= 4;
-    }
+    int nr = 0, why = 0; info[i] = 0;
+    const float b0 = stats16[STAT_STAGEB];
+    int rc = entry_step_fast<true>(c, state, N, i, env_offset + i, action + (size_t)i * 7, obs + (size_t)i * JACO_NOBS, reward + i, done + i, succ + i, wb + i, 0, auto_reset, stats16, &nr, &why, &ws, true);
+    if (stats16[STAT_STAGEB] != b0) info[i] |= 1;
+    if (rc == FAST_OK) { if (nr) { entry_reset(c, state, N, i, env_offset + i, obs + (size_t)i * JACO_NOBS); stats16[STAT_GENRESET] += 1; info[i] |= 4; } }
+    else { entry_step(c, state, N, i, env_offset + i, action + (size_t)i * 7, obs + (size_t)i * JACO_NOBS, reward + i, done + i, succ + i, wb + i, 0, auto_reset, stats16); stats16[STAT_FALLBACK] += 1; info[i] |= 2; }
   }
-  for (int k = 0; k < 16; k++) stats16[k] += local[k] + (float)gstats[k];
 }
-extern "C" int hh_sizeof_piperec() { return (int)sizeof(PipeRec); }

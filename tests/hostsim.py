@@ -73,15 +73,16 @@ class HostSim:
                             fp(wb), int(auto_reset), fp(self.stats), why.ctypes.data_as(C.POINTER(C.c_int)), int(allow_fallback))
         return obs, rew, done, succ, wb, why
 
-    def step_pipe(self, action, auto_reset=False):
-        """The production pipeline (jaco_pipe.cuh) emulated sequentially; returns (..., info) with per-env path bits."""
+    def step_hybrid(self, action, auto_reset=False):
+        """The production env step (jaco_kernel_coop.cu) emulated sequentially; returns (..., info) with per-env path bits
+        (1 = served by the cooperative path, 2 = general-path fall-back, 4 = general reset)."""
         a = np.zeros((self.n, 7), np.float32)
         a[:, : action.shape[1]] = action
         obs = np.zeros((self.n, NOBS), np.float32)
         rew, wb = np.zeros(self.n, np.float32), np.zeros(self.n, np.float32)
         done, succ = np.zeros(self.n, np.uint8), np.zeros(self.n, np.uint8)
         info = np.zeros(self.n, np.int32)
-        self.L.hh_step_pipe(self.task, self.variant, C.c_ulonglong(self.seed), self.env_offset, fp(self.state), self.n, fp(a), fp(obs),
+        self.L.hh_step_hybrid(self.task, self.variant, C.c_ulonglong(self.seed), self.env_offset, fp(self.state), self.n, fp(a), fp(obs),
                             fp(rew), done.ctypes.data_as(C.POINTER(C.c_ubyte)), succ.ctypes.data_as(C.POINTER(C.c_ubyte)),
                             fp(wb), int(auto_reset), fp(self.stats), info.ctypes.data_as(C.POINTER(C.c_int)))
         return obs, rew, done, succ, wb, info

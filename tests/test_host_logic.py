@@ -215,11 +215,11 @@ def test_osc_pinv_branch_near_singularity():
     assert n_pinv >= 10
 
 
-# ------------------------------------------------------------------------------------------- production pipeline
-# The per-substep pipeline (mujoco_jaco_b200/csrc/jaco_pipe.cuh: K_S / K_B / K_S' / K_E) emulated sequentially on the
-# CPU by tests/harness with the launch order of jaco_kernel_pipe.cu.
+# ------------------------------------------------------------------------------------------- production step protocol
+# The production env step (mujoco_jaco_b200/csrc/jaco_kernel_coop.cu: hybrid path for every env, then the general path for
+# what it hands back) emulated sequentially on the CPU by tests/harness with the device's protocol.
 
-def test_pipeline_env_step_matches_oracle_picking():
+def test_hybrid_env_step_matches_oracle_picking():
     n = 48
     hs = HostSim(n, task="picking", seed=21)
     hs.reset()
@@ -230,7 +230,7 @@ def test_pipeline_env_step_matches_oracle_picking():
     dirty = 0
     for step in range(4):
         a = rng.uniform(-1, 1, (n, 7)).astype(np.float32)
-        obs, rew, done, succ, wb, info = hs.step_pipe(a)
+        obs, rew, done, succ, wb, info = hs.step_hybrid(a)
         dirty += int((info & 1).sum())
         ref = [o.step(a[i].astype(np.float64)) for i, o in enumerate(ora)]
         robs = np.stack([x[0] for x in ref]); rrew = np.array([x[1] for x in ref])
@@ -240,25 +240,26 @@ def test_pipeline_env_step_matches_oracle_picking():
         assert np.array_equal(succ, np.array([x[3] for x in ref]))
         assert np.abs(wb - np.array([x[4] for x in ref])).max() < 1e-4
         assert not (info & 2).any()                 # nothing handed back to the general path
-    assert dirty > 0                                # some envs did go through the dirty stream (K_B / K_S')
+    assert dirty > 0                                # some envs were served by the cooperative path
 
 
-def test_pipeline_matches_fused_hybrid_path():
-    """Same arithmetic, different schedule: the pipeline against the round-1 fused hybrid step on an ageing population."""
+def test_hybrid_matches_bail_and_fall_back_path():
+    """Same arithmetic, different schedule: the hybrid path against the bail-only fast path with general-path fall-back, on an
+    ageing population."""
     n = 64
     a_, b_ = HostSim(n, task="picking", seed=0), HostSim(n, task="picking", seed=0)
     a_.reset(); b_.reset()
     rng = np.random.default_rng(0)
     for step in range(12):
         a = rng.uniform(-1, 1, (n, 7)).astype(np.float32)
-        o1, r1, d1, s1, w1, why = a_.step_fast(a, auto_reset=True, allow_fallback=2)
-        o2, r2, d2, s2, w2, info = b_.step_pipe(a, auto_reset=True)
+        o1, r1, d1, s1, w1, why = a_.step_fast(a, auto_reset=True, allow_fallback=1)
+        o2, r2, d2, s2, w2, info = b_.step_hybrid(a, auto_reset=True)
         assert np.abs(o1 - o2).max() < 2e-5 and np.abs(r1 - r2).max() < 1e-5
         assert np.array_equal(d1, d2) and np.array_equal(s1, s2)
     assert b_.stats[7] == 12 * n and b_.stats[11] > 0      # env steps counted, stage-B tasks served
 
 
-def test_pipeline_terminal_logic_and_in_kernel_reset():
+def test_hybrid_terminal_logic_and_in_place_reset():
     hs = HostSim(4, task="picking", seed=2)
     hs.reset()
     q, v, aux = hs.get_state()
@@ -266,7 +267,7 @@ def test_pipeline_terminal_logic_and_in_kernel_reset():
     aux[1, 9] = 699                                     # env 1: time-out on this step
     q[2, 2] = np.pi; aux[2, 46 + 2] = np.pi              # env 2: singular posture
     hs.set_state(q, v, aux)
-    obs, rew, done, succ, wb, info = hs.step_pipe(np.zeros((4, 7), np.float32), auto_reset=True)
+    obs, rew, done, succ, wb, info = hs.step_hybrid(np.zeros((4, 7), np.float32), auto_reset=True)
     assert done[0] == 1 and rew[0] < -19
     assert done[1] == 1 and -10.2 < rew[1] < -9.8 and wb[1] == 0
     assert done[2] == 1 and -1.2 < rew[2] < -0.8
@@ -291,7 +292,7 @@ def test_pipeline_terminal_logic_and_in_kernel_reset():
 def test_reaching_sends_zero_finger_command_after_first_action():
     """util:37,76-79,625-626: with a 6-D action gripper_angle_array is never refilled and stays zeros, so once action_in
     is set the finger servos are commanded 0.0 (obs[7] keeps showing gripper_angle = 0.6).  Oracle, general path and
-    pipeline must agree on the finger joints after one step."""
+    the hybrid step must agree on the finger joints after one step."""
     n = 6
     act = np.random.default_rng(4).uniform(-1, 1, (n, 6)).astype(np.float32)
     hg = HostSim(n, task="reaching", seed=8); hg.reset()
@@ -300,7 +301,7 @@ def test_reaching_sends_zero_finger_command_after_first_action():
     for o in ora:
         o.reset()
     q0 = hg.get_state()[0][:, 6:9].copy()
-    og = hg.step(act); op = hp.step_pipe(act)
+    og = hg.step(act); op = hp.step_hybrid(act)
     oq = np.stack([o.step(act[i].astype(np.float64)) and o.get_state()[0] for i, o in enumerate(ora)])
     qg, qp = hg.get_state()[0], hp.get_state()[0]
     assert np.abs(qg[:, 6:9] - oq[:, 6:9]).max() < 1e-5 and np.abs(qp[:, 6:9] - oq[:, 6:9]).max() < 1e-5
