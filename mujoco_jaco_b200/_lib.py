@@ -14,11 +14,12 @@ DIAG_UNITS = []
 HEADERS = [os.path.join(CSRC, f) for f in ("jaco_sim.cuh", "jaco_fast.cuh", "jaco_coop.cuh", "jaco_launch.h", "jaco_model.h")] + [
     os.path.join(REPO, "include", "jaco_b200.h"), os.path.join(REPO, "include", "jaco_model_layout.h")]
 SOURCES = [os.path.join(CSRC, u) for u in UNITS] + HEADERS
-# -prec-div=false -prec-sqrt=false -ftz=true: 2-ulp division / square root and flushed denormals.  IEEE division and
-# sqrt expand to ~10-instruction sequences with slow-path calls; in this instruction-issue-bound kernel they were
-# 20 % of the step (52 -> 40 ms per 65 536-env step).  The parity bars (1e-4 rel / 1e-6 abs one-step state, 1e-5
-# reward) are three orders of magnitude above the added rounding error; the GPU parity suite runs with these flags.
-NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-prec-div=false", "-prec-sqrt=false",
+# -prec-div=false -ftz=true: 2-ulp division and flushed denormals.  IEEE division expands to ~10-instruction sequences with
+# slow-path calls; in this instruction-delivery-bound kernel it costs 10 ms of a 46 ms aged step.  The square root stays IEEE
+# (-prec-sqrt=true, +1.7 ms): with the 2-ulp square root one of the 4096 in-contact snapshots left the observation bar after
+# one env step (EE pose off by 26 um; 0.7 um with the IEEE root) although every conditioning probe of the test-suite calls it
+# well-conditioned -- profiles/r02_fastmath_flags.log.  The GPU parity suite runs with exactly these flags.
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-prec-div=false", "-prec-sqrt=true",
               "-ftz=true", "-Xcompiler", "-fPIC"]
 
 SYMBOLS = ["jaco_create", "jaco_destroy", "jaco_last_error", "jaco_reset", "jaco_step", "jaco_step_host",

@@ -177,6 +177,8 @@ struct jo_env {
   real M[NV][NV], bias[NV], qfrc_smooth[NV], qacc_smooth[NV], qacc[NV], qfrc_constraint[NV];
   real ee_pos[3], ee_quat[4], Jee[6][6], obj_xpos[3];
   real sensordata[20];
+  int touch_knife_edge;   /* test probe: see touch_sensors */
+  int probe, contact_knife_edge; real margin_shift;   /* test probe (jo_set_probe): contact count of the last forward under margins +-2 um */
   int ncon, nefc, solver_iters; real solver_grad;
   contact_t con[JO_MAXCON];
   real w_jar[JO_MAXEFC], w_jp[JO_MAXEFC], w_bp[JO_MAXEFC];
@@ -572,15 +574,15 @@ static void collision(jo_env *e) {
     geom_world(e, P->g1, p1, R1); geom_world(e, P->g2, p2, R2);
     if (P->group >= 1 && P->group <= 4) { /* cull the whole hand cluster at once */
       const geom_t *O = (P->group == 1) ? G2 : G1; const real *po = (P->group == 1) ? p2 : p1;
-      if (O->type != G_PLANE) { real d[3]; v3sub(d, hs, po); if (v3norm(d) > e->hand_sphere[3] + O->rbound + P->margin) continue; }
-      else { real d[3]; v3sub(d, hs, po); if (d[2] > e->hand_sphere[3] + P->margin) continue; }
+      if (O->type != G_PLANE) { real d[3]; v3sub(d, hs, po); if (v3norm(d) > e->hand_sphere[3] + O->rbound + (P->margin + e->margin_shift)) continue; }
+      else { real d[3]; v3sub(d, hs, po); if (d[2] > e->hand_sphere[3] + (P->margin + e->margin_shift)) continue; }
     }
-    if (G1->type != G_PLANE && G2->type != G_PLANE) { real d[3]; v3sub(d, p1, p2); if (v3norm(d) > G1->rbound + G2->rbound + P->margin) continue; }
-    if (G1->type == G_PLANE && G2->type == G_BOX) collide_plane_box(e, p, p1, R1, p2, R2, G2->size, P->margin);
-    else if (G1->type == G_PLANE && G2->type == G_CAPSULE) collide_plane_capsule(e, p, p1, R1, p2, R2, G2->size, P->margin);
-    else if (G1->type == G_BOX && G2->type == G_BOX) collide_box_box(e, p, p1, R1, G1->size, p2, R2, G2->size, P->margin);
-    else if (G1->type == G_BOX && G2->type == G_CAPSULE) collide_capsule_box(e, p, 1, p2, R2, G2->size, p1, R1, G1->size, P->margin);
-    else if (G1->type == G_CAPSULE && G2->type == G_BOX) collide_capsule_box(e, p, 0, p1, R1, G1->size, p2, R2, G2->size, P->margin);
+    if (G1->type != G_PLANE && G2->type != G_PLANE) { real d[3]; v3sub(d, p1, p2); if (v3norm(d) > G1->rbound + G2->rbound + (P->margin + e->margin_shift)) continue; }
+    if (G1->type == G_PLANE && G2->type == G_BOX) collide_plane_box(e, p, p1, R1, p2, R2, G2->size, (P->margin + e->margin_shift));
+    else if (G1->type == G_PLANE && G2->type == G_CAPSULE) collide_plane_capsule(e, p, p1, R1, p2, R2, G2->size, (P->margin + e->margin_shift));
+    else if (G1->type == G_BOX && G2->type == G_BOX) collide_box_box(e, p, p1, R1, G1->size, p2, R2, G2->size, (P->margin + e->margin_shift));
+    else if (G1->type == G_BOX && G2->type == G_CAPSULE) collide_capsule_box(e, p, 1, p2, R2, G2->size, p1, R1, G1->size, (P->margin + e->margin_shift));
+    else if (G1->type == G_CAPSULE && G2->type == G_BOX) collide_capsule_box(e, p, 0, p1, R1, G1->size, p2, R2, G2->size, (P->margin + e->margin_shift));
   }
 }
 
@@ -741,6 +743,7 @@ static int ray_hits_site(const site_t *S, const real *spos, const real *sR, cons
 }
 /* mjSENS_TOUCH: sum of normal forces of contacts on the site's body whose force ray meets the site volume */
 static void touch_sensors(jo_env *e) {
+  e->touch_knife_edge = 0;
   for (int c = 0; c < e->ncon; c++) {
     contact_t *con = &e->con[c]; real f = 0;
     int nr = con->dim == 1 ? 1 : 2 * (con->dim - 1);
@@ -758,6 +761,12 @@ static void touch_sensors(jo_env *e) {
       real ray[3]; real sg = con->g1 == S->geom ? R_(1) : R_(-1);
       for (int i = 0; i < 3; i++) ray[i] = sg * con->frame[i];
       if (ray_hits_site(S, spos, sR, con->pos, ray)) sum += con->nforce;
+      { /* knife-edge probe for the parity tests: does the decision change when the site grows / shrinks by 2 um?  (pad geoms and
+           their sensor sites have the same lateral size, so a contact at a pad edge sits exactly on the site boundary) */
+        site_t big = *S, small = *S;
+        for (int i = 0; i < 3; i++) { big.size[i] += R_(2e-6); small.size[i] -= R_(2e-6); }
+        if (ray_hits_site(&big, spos, sR, con->pos, ray) != ray_hits_site(&small, spos, sR, con->pos, ray)) e->touch_knife_edge = 1;
+      }
     }
     e->sensordata[s] = sum;
   }
@@ -784,6 +793,11 @@ static void ee_quaternion(const jo_env *e, const real *qpos, real *q) {
 static void mj_forward(jo_env *e) {
   kinematics(e);
   mass_matrix(e);
+  if (e->probe) { /* parity-test probe: is a geom pair within 2 um of making / breaking contact at this state? */
+    e->margin_shift = R_(2e-6); collision(e); int np_ = e->ncon;
+    e->margin_shift = R_(-2e-6); collision(e); int nm_ = e->ncon;
+    e->margin_shift = 0; e->contact_knife_edge = np_ != nm_;
+  }
   collision(e);
   rne_bias(e);
   real act[NV];
@@ -827,6 +841,10 @@ static void mj_euler(jo_env *e) {
 static void mj_step_(jo_env *e) { mj_forward(e); mj_euler(e); }
 
 /* ------------------------------------------------------------------------------------------- OSC (App. A.2) */
+/* parity-test probe (jo_osc_knife_edge): set when an OSC call sits on a decision boundary that float32 rounding may take either way:
+   |det(J M^-1 J^T)| within 2 % of the 1e-3 branch threshold, an eigenvalue of the pinv branch within 30 % of the rcond cut-off, or the
+   orientation error within 1e-4 of 180 degrees (sign flip of the error vector) */
+static int g_osc_knife_edge = 0;
 /* symmetric pseudo-inverse via cyclic Jacobi (numpy.linalg.pinv(X, rcond) for symmetric PSD X) */
 static void sym_pinv6(const real *X, real rcond, real *out) {
   real A[6][6], V[6][6];
@@ -844,6 +862,7 @@ static void sym_pinv6(const real *X, real rcond, real *out) {
     }
   }
   real lmax = 0; for (int i = 0; i < 6; i++) if (rabs(A[i][i]) > lmax) lmax = rabs(A[i][i]);
+  for (int k = 0; k < 6; k++) { real ratio = rabs(A[k][k]) / (lmax > 0 ? lmax : 1); if (ratio > R_(0.7) * rcond && ratio < R_(1.3) * rcond) g_osc_knife_edge = 1; }
   for (int i = 0; i < 6; i++) for (int j = 0; j < 6; j++) {
     real s = 0;
     for (int k = 0; k < 6; k++) if (rabs(A[k][k]) > rcond * lmax) s += V[i][k] * V[j][k] / A[k][k];
@@ -859,6 +878,7 @@ static void osc_generate(const real J[6][6], const real M[6][6], const real *bia
   real Lx[6][6]; memcpy(Lx, X, sizeof Lx);
   int ok = chol_factor(&Lx[0][0], 6, 6); real det = 1;
   if (ok) for (int i = 0; i < 6; i++) det *= Lx[i][i] * Lx[i][i];
+  if (ok && rabs(det) > R_(0.98e-3) && rabs(det) < R_(1.02e-3)) g_osc_knife_edge = 1;
   if (ok && rabs(det) >= R_(1e-3)) {
     for (int c = 0; c < 6; c++) { real col[6] = {0}; col[c] = 1; chol_solve(&Lx[0][0], 6, 6, col); for (int r = 0; r < 6; r++) Mx[r][c] = col[r]; }
   } else sym_pinv6(&X[0][0], R_(1e-4), &Mx[0][0]);
@@ -869,6 +889,7 @@ static void osc_generate(const real J[6][6], const real M[6][6], const real *bia
   { real n = rsqrt_(qd[0] * qd[0] + qd[1] * qd[1] + qd[2] * qd[2] + qd[3] * qd[3]); for (int i = 0; i < 4; i++) qd[i] /= n; }
   quat_mul(qr, qd, qc);
   real sg = qr[0] > 0 ? R_(1) : (qr[0] < 0 ? R_(-1) : R_(0));
+  if (rabs(qr[0]) < R_(1e-4)) g_osc_knife_edge = 1;   /* orientation error at 180 deg: the sign of the error vector is a coin flip */
   for (int i = 0; i < 3; i++) ut[3 + i] = -qr[1 + i] * sg;
   /* velocity limiting */
   real sat_xyz = vmax0 / kp * kv, sat_abg = vmax1 / ko * kv, nx = v3norm(ut), na = v3norm(ut + 3), sc[6] = {1, 1, 1, 1, 1, 1};
@@ -1226,6 +1247,13 @@ void jo_osc(const jo_env *e, const double *J, const double *M, const double *bia
   osc_generate(J_, M_, b_, p_, q_, d_, t_, u_);
   for (int i = 0; i < 6; i++) u[i] = u_[i];
 }
+/* 1 when, in the last forward, some contact's touch-sensor attribution flips if the sensor site is resized by +-2 um */
+/* 1 when an OSC call since the last jo_osc_knife_edge_clear sat on the pinv branch threshold / rcond cut-off (process-wide flag) */
+int jo_osc_knife_edge(void) { return g_osc_knife_edge; }
+void jo_osc_knife_edge_clear(void) { g_osc_knife_edge = 0; }
+int jo_touch_knife_edge(const jo_env *e) { return e->touch_knife_edge | (e->probe ? e->contact_knife_edge : 0); }
+/* enables the (slower) contact-margin probe evaluated by every forward */
+void jo_set_probe(jo_env *e, int on) { e->probe = on; e->margin_shift = 0; e->contact_knife_edge = 0; }
 void jo_solver_stats(const jo_env *e, int *iters, double *gradnorm, int *nefc) {
   if (iters) *iters = e->solver_iters; if (gradnorm) *gradnorm = e->solver_grad; if (nefc) *nefc = e->nefc;
 }

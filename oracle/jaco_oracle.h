@@ -52,6 +52,14 @@ int jo_get_contacts(const jo_env *e, double *out10, int maxcon);
 /* abr_control OSC.generate on explicit inputs (App. A.2) */
 void jo_osc(const jo_env *e, const double *J6x6, const double *M6x6, const double *bias6, const double *ee_pos,
             const double *ee_quat, const double *dq6, const double *target6, double *u6);
+/* parity-test probe: 1 when a touch-sensor attribution of the last forward flips if the site is resized by +-2 um */
+int jo_touch_knife_edge(const jo_env *e);
+/* parity-test probe: an OSC call since the last clear sat within 2 % of the |det| < 1e-3 branch threshold or had an eigenvalue within
+   30 % of the rcond = 1e-4 cut-off of numpy.linalg.pinv (process-wide flag) */
+int jo_osc_knife_edge(void);
+void jo_osc_knife_edge_clear(void);
+/* also report (through jo_touch_knife_edge) whether a geom pair is within 2 um of making / breaking contact in the last forward */
+void jo_set_probe(jo_env *e, int on);
 /* solver statistics of the last forward */
 void jo_solver_stats(const jo_env *e, int *iters, double *gradnorm, int *nefc);
 /* Philox4x32-10 uniforms, exposed so the tests can pin the generator */

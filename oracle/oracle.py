@@ -53,6 +53,10 @@ def lib(f32=False):
         L.jo_get_contacts.restype = C.c_int
         L.jo_osc.argtypes = [C.c_void_p] + [_dp] * 8
         L.jo_solver_stats.argtypes = [C.c_void_p, _ip, _dp, _ip]
+        L.jo_touch_knife_edge.argtypes = [C.c_void_p]
+        L.jo_set_probe.argtypes = [C.c_void_p, C.c_int]
+        L.jo_osc_knife_edge.argtypes = []
+        L.jo_osc_knife_edge_clear.argtypes = []
         L.jo_philox.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32)]
         _libs[name] = L
     return _libs[name]
@@ -129,6 +133,22 @@ class OracleEnv:
         args = [np.ascontiguousarray(x, np.float64) for x in (J, M, bias, ee_pos, ee_quat, dq, target)]
         self.L.jo_osc(self.h, *[_d(x) for x in args], _d(u))
         return u
+
+    def set_probe(self, on=True):
+        """enable the contact-margin probe (every forward also collides with margins +-2 um)"""
+        self.L.jo_set_probe(self.h, int(on))
+
+    def osc_knife_edge(self, clear=True):
+        """True when an OSC call since the last clear sat on the pinv branch threshold or the rcond cut-off (process-wide flag)"""
+        r = bool(self.L.jo_osc_knife_edge())
+        if clear:
+            self.L.jo_osc_knife_edge_clear()
+        return r
+
+    def touch_knife_edge(self):
+        """True when a touch-sensor attribution of the last forward flips if the sensor site is resized by +-2 um, or (with
+        set_probe) a geom pair is within 2 um of making / breaking contact"""
+        return bool(self.L.jo_touch_knife_edge(self.h))
 
     def solver_stats(self):
         it, n = C.c_int(), C.c_int()

@@ -1,11 +1,15 @@
 """GPU parity tests proper: the CUDA path (through the C ABI) against the CPU oracle on identical inputs.
 
 Tolerances (BASELINE.json north_star): one-step state 1e-4 relative / 1e-6 absolute in fp32, reward 1e-5,
-contact count / success / done bit-exact.  The oracle is fp64; a mismatch budget of 1% of envs is allowed for
-discrete outcomes whose inputs sit within fp32 rounding of a decision boundary (reported, never hidden).
+contact count / success / done bit-exact.  No percentage budgets: an env is excused from a check only by the explicit
+oracle-side knife-edge predicate of tests/parity_util.py (the float32 build of the ORACLE flips the outcome / leaves the
+bar on that input); the excluded counts are printed and bounded.  In-contact snapshots, config 2 at 4096 envs, terminal
+boundaries and the pinv branch: test_gpu_contact_parity.py.
 """
 import numpy as np
 import pytest
+
+from parity_util import ATOL, H, RTOL, block_scale, check_step, check_substep, close, live_answers_and_knife_edges
 
 torch = pytest.importorskip("torch")
 pytestmark = pytest.mark.gpu
@@ -37,55 +41,47 @@ def test_reset_matches_oracle(task):
 
 
 def test_one_substep_state_and_contacts_picking():
-    """mj_step from identical (qpos, qvel, ctrl): state within 1e-4 rel / 1e-6 abs, ncon bit-exact."""
+    """mj_step from identical (qpos, qvel, ctrl): state within 1e-4 rel / 1e-6 abs, ncon / touch flags bit-exact, qacc."""
     from mujoco_jaco_b200.env import JacoVecEnv
     n = 512
     env = JacoVecEnv(n, task="picking", seed=9, auto_reset=False)
     env.reset()
-    # one zero-action env step first: at the reset pose the destination box touches the floor with dist == 0
-    # exactly, a knife edge on which fp32 (contact) and the fp64 oracle (no contact) legitimately differ
+    # one zero-action env step first: at the reset pose the destination box touches the floor with dist == 0 exactly, a
+    # knife edge on which fp32 (contact) and the fp64 oracle (no contact) legitimately differ
     env.step(torch.zeros(n, 7, device="cuda"))
-    q, v, aux = [t.cpu().numpy().astype(np.float64) for t in env.get_state()]
+    q, v, aux = [t_.cpu().numpy() for t_ in env.get_state()]
     rng = np.random.default_rng(1)
-    v[:, :9] = rng.normal(0, 0.3, (n, 9))
-    ctrl = np.concatenate([rng.uniform(-5, 5, (n, 6)), rng.uniform(0.6, 1.0, (n, 1)).repeat(3, 1)], 1)
+    v[:, :9] = rng.normal(0, 0.3, (n, 9)).astype(np.float32)
+    aux = aux[:, :64]
+    ctrl = np.concatenate([rng.uniform(-5, 5, (n, 6)), rng.uniform(0.6, 1.0, (n, 1)).repeat(3, 1)], 1).astype(np.float32)
+    o64, (kd, kc), _ = live_answers_and_knife_edges("picking", q, v, aux, ctrl=ctrl, seed=9)
     env.set_state(torch.tensor(q), torch.tensor(v), torch.tensor(aux))
-    ncon, sd, qacc = env.debug_substep(torch.tensor(ctrl))
-    q1, v1, _ = [t.cpu().numpy() for t in env.get_state()]
-    ora = _oracles("picking", 9, n)
-    bad_state = bad_ncon = 0
-    for i, o in enumerate(ora):
-        o.set_state(q[i].astype(np.float32).astype(np.float64), v[i].astype(np.float32).astype(np.float64), aux[i, :64])
-        nc, osd = o.mj_step(ctrl[i].astype(np.float32).astype(np.float64))
-        oq, ov, _ = o.get_state()
-        bad_ncon += int(nc != int(ncon[i]))
-        ok = _close(q1[i], oq, 1e-4, 1e-6).all() and _close(v1[i], ov, 1e-4, 2e-5).all()
-        bad_state += int(not ok)
-    assert bad_ncon <= n // 100, f"contact count mismatch on {bad_ncon}/{n} envs"
-    assert bad_state <= n // 100, f"one-substep state mismatch on {bad_state}/{n} envs"
+    ncon, sd, qacc = [t_.cpu().numpy() for t_ in env.debug_substep(torch.tensor(ctrl))]
+    q1, v1, _ = [t_.cpu().numpy() for t_ in env.get_state()]
+    # the object rests on the holder and the destination box on the floor: in-contact bars of check_substep (ncon / touch
+    # flags exact, qpos strict, second-tier bound on the velocities of the bodies in contact)
+    check_substep("picking after reset + 1 step, random joint velocities", dict(qpos=q1, qvel=v1, ncon=ncon, sensordata=sd, qacc=qacc), o64, kd, kc)
+    arm = ~kd    # the arm itself is contact-free here: its 9 dofs meet the strict bar relative to the block scale of qacc
+    sc = block_scale(o64["sub_qacc"])
+    assert close(v1[:, :9], o64["sub_qvel"][:, :9], RTOL, ATOL, (H * sc)[:, :9])[arm].all()
 
 
 def test_env_step_reward_done_picking():
+    """Three env steps of a random roll-out; before each step the kernel's state is injected into the oracle, so every step is a
+    one-step comparison from identical inputs: done / succ / touch bit-exact, reward 1e-5, observation."""
     from mujoco_jaco_b200.env import JacoVecEnv
     n = 256
     env = JacoVecEnv(n, task="picking", seed=21, auto_reset=False)
     env.reset()
-    ora = _oracles("picking", 21, n)
-    for o in ora:
-        o.reset()
+    env.step(torch.zeros(n, 7, device="cuda"))      # leave the dist == 0 knife edge of the reset pose (see above)
     rng = np.random.default_rng(3)
     for step in range(3):
+        q, v, aux = [t_.cpu().numpy() for t_ in env.get_state()]
         a = rng.uniform(-1, 1, (n, 7)).astype(np.float32)
-        obs, rew, done, succ = [t.cpu().numpy() for t in env.step(torch.from_numpy(a).cuda())]
-        ref = [o.step(a[i].astype(np.float64)) for i, o in enumerate(ora)]
-        robs = np.stack([x[0] for x in ref]); rrew = np.array([x[1] for x in ref])
-        rdone = np.array([x[2] for x in ref]); rsucc = np.array([x[3] for x in ref])
-        env_bad = (np.abs(obs - robs).max(1) > 1e-3) | (np.abs(rew - rrew) > 1e-4)
-        assert env_bad.mean() <= 0.02, f"step {step}: {env_bad.sum()} envs off"
-        assert (done.astype(bool) != rdone).mean() <= 0.01
-        assert (succ != rsucc).mean() <= 0.01
-        good = ~env_bad
-        assert np.abs(rew[good] - rrew[good]).max() < 1e-5 * 10
+        o64, _, (kd, kc) = live_answers_and_knife_edges("picking", q, v, aux[:, :64], act=a, seed=21)
+        obs, rew, done, succ = [t_.cpu().numpy() for t_ in env.step(torch.from_numpy(a).cuda())]
+        assert kc.mean() < 0.05
+        check_step(f"roll-out step {step}", dict(obs=obs, reward=rew, done=done, succ=succ), o64, kd, kc)
 
 
 def test_rollout_50_steps_reaching_drift():
@@ -142,7 +138,7 @@ def test_single_env_shim_runs_1000_random_steps(tmp_path):
     assert obs.shape == (26,) and obs.dtype == np.float32
     rng = np.random.default_rng(0)
     ndone = 0
-    for _ in range(300):
+    for _ in range(1000):
         obs, r, d, info = env.step(rng.uniform(-1, 1, 7))
         assert obs.shape == (26,) and np.isfinite(obs).all() and np.isfinite(r) and info == {0: 0}
         if d:
@@ -153,24 +149,29 @@ def test_single_env_shim_runs_1000_random_steps(tmp_path):
 
 @pytest.mark.parametrize("task,variant", [("placing", "base"), ("pickAndplace", "cis"), ("picking", "trans"), ("placing", "cis")])
 def test_config4_tasks_and_variants_one_step(task, variant):
-    """BASELINE config 4: placing / pickAndplace and the _cis / _trans variants (base-relative observations,
-    a/100 - a/20 action scale, 3-tuple terminal logic): reset (placing = 150 in-hand settle substeps) and one env
-    step against the oracle.  Placing starts with the object held between the fingers (contact-rich, chaotic), so
-    the bar is on the fraction of envs that agree."""
+    """BASELINE config 4: placing / pickAndplace and the _cis / _trans variants (base-relative observations, a/100 - a/20
+    action scale, 3-tuple terminal logic): reset (placing = 150 in-hand settle substeps) and one env step against the oracle.
+    Placing starts with the object held between the fingers: its 150-substep settle is compared on the envs where the oracle's
+    own float32 build reproduces its float64 reset; the env step is a one-step comparison from the kernel's injected state."""
     from mujoco_jaco_b200.env import JacoVecEnv
     n = 64
     env = JacoVecEnv(n, task=task, variant=variant, seed=13, auto_reset=False)
     obs = env.reset().cpu().numpy()
     ora = _oracles(task, 13, n, variant=variant)
     oobs = np.stack([o.reset() for o in ora])
-    bad_reset = np.abs(obs - oobs).max(1) > (2e-3 if task == "placing" else 5e-6)
-    assert bad_reset.mean() <= (0.1 if task == "placing" else 0.0), f"reset: {bad_reset.sum()} of {n} envs off"
+    tol = 2e-3 if task == "placing" else 5e-6
+    if task == "placing":
+        o32 = np.stack([o.reset() for o in _oracles(task, 13, n, variant=variant, f32=True)])
+        ke = np.abs(o32 - oobs).max(1) > tol / 4     # the settle is chaotic there: float32 rounding alone moves it
+        print(f"placing reset: {int(ke.sum())} of {n} envs excluded (oracle float32 vs float64 reset differ)")
+        assert ke.mean() < 0.3
+    else:
+        ke = np.zeros(n, bool)
+    assert (np.abs(obs - oobs).max(1) <= tol)[~ke].all(), np.abs(obs - oobs).max(1)
+    if task != "placing":
+        env.step(torch.zeros(n, 7, device="cuda"))  # leave the dist == 0 knife edge of the reset pose
+    q, v, aux = [t_.cpu().numpy() for t_ in env.get_state()]
     a = np.random.default_rng(17).uniform(-1, 1, (n, 7)).astype(np.float32)
-    o1, r1, d1, s1 = [t.cpu().numpy() for t in env.step(torch.from_numpy(a).cuda())]
-    ref = [o.step(a[i].astype(np.float64)) for i, o in enumerate(ora)]
-    ro = np.stack([x[0] for x in ref]); rr = np.array([x[1] for x in ref]); rd = np.array([x[2] for x in ref])
-    good = ~bad_reset
-    tol = 5e-3 if task == "placing" else 1e-3
-    off = (np.abs(o1 - ro).max(1) > tol) | (np.abs(r1 - rr) > 1e-3)
-    assert off[good].mean() <= (0.15 if task == "placing" else 0.03), f"step: {off[good].sum()} of {good.sum()} envs off"
-    assert (d1.astype(bool) != rd)[good].mean() <= 0.03
+    o64, _, (kd, kc) = live_answers_and_knife_edges(task, q, v, aux[:, :64], act=a, variant=variant, seed=13)
+    o1, r1, d1, s1 = [t_.cpu().numpy() for t_ in env.step(torch.from_numpy(a).cuda())]
+    check_step(f"{task}/{variant}", dict(obs=o1, reward=r1, done=d1, succ=s1), o64, kd, kc, max_discrete_frac=0.35 if task == "placing" else 0.1)
