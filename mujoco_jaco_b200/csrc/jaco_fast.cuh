@@ -1279,7 +1279,11 @@ JHD JNOINLINE int fast_reset(const JacoCfg& cfg, FastSim& s, int env_id, float* 
   ChainOut c;
   const float O0[3] = {0, 0, 0.5f};
   fast_chain<true>(s.qpos, s.qvel, O0, &sb, c);
-  if (c.near) return 0;
+  if (c.near) {   // bounding spheres overlap: the owner-thread narrow phase decides; only a real arm contact needs the general reset
+    LocalSink ks; ks.ncon = 0;
+    fast_arm_collide(c, fo, fd, ks);
+    if (ks.ncon > 0) return 0;
+  }
   for (int k = 0; k < 9; k++) if (MDL.ch_limited[k] && (s.qpos[k] - MDL.ch_range[k][0] < 0 || MDL.ch_range[k][1] - s.qpos[k] < 0)) return 0;
   v3copy(s.eepos, c.eepos);
   for (int i = 0; i < 4; i++) s.eeq[i] = c.eeq[i];

@@ -7,19 +7,11 @@ per-env Philox streams, so a sharded run reproduces the single-process run env f
 """
 from __future__ import annotations
 
-import os
-
 import torch
 import torch.distributed as dist
 
 STAT_NAMES = ["episodes", "successes", "return_sum", "timeouts", "drops", "singular_exits", "nan_resets",
               "env_steps", "length_sum"]
-
-
-def rank_world():
-    """(rank, world, local_rank) from the torchrun environment (defaults: single process)."""
-    return (int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")),
-            int(os.environ.get("LOCAL_RANK", "0")))
 
 
 def shard_range(rank: int, world: int, n_per_rank: int):
@@ -44,11 +36,11 @@ def max_over_ranks(value: float, device=None, group=None) -> float:
     return float(t.item())
 
 
-def summarize(stats: torch.Tensor) -> dict:
-    s = stats.detach().cpu().tolist()
-    out = {k: s[i] for i, k in enumerate(STAT_NAMES)}
-    ep = max(out["episodes"], 1.0)
-    out["success_rate"] = out["successes"] / ep
-    out["mean_return"] = out["return_sum"] / ep
-    out["mean_length"] = out["length_sum"] / ep
-    return out
+def gather_per_rank(vec: torch.Tensor, group=None):
+    """The same small float vector from every rank as a list of lists (rank order); [vec] without a process group.  Used by
+    bench.py for its per-rank table (step time, workload fractions): evidence, not a data-path exchange."""
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        out = [torch.zeros_like(vec) for _ in range(dist.get_world_size(group))]
+        dist.all_gather(out, vec, group=group)
+        return [o.cpu().tolist() for o in out]
+    return [vec.cpu().tolist()]

@@ -33,12 +33,21 @@ def load_blob():
 _libs = {}
 
 
-def lib(f32=False):
-    name = "libjaco_oracle_f32.so" if f32 else "libjaco_oracle.so"
+def build_fast():
+    """-O3 -march=native build for the CPU baseline; built on the machine that times it.  Returns True on success."""
+    try:
+        subprocess.check_call(["make", "-s", "-C", HERE, "fast"])
+        return os.path.exists(os.path.join(HERE, "libjaco_oracle_fast.so"))
+    except Exception:
+        return False
+
+
+def lib(f32=False, fast=False):
+    name = "libjaco_oracle_fast.so" if fast else ("libjaco_oracle_f32.so" if f32 else "libjaco_oracle.so")
     if name not in _libs:
         path = os.path.join(HERE, name)
         if not os.path.exists(path):
-            build()
+            build_fast() if fast else build()
         L = C.CDLL(path)
         L.jo_create.restype = C.c_void_p
         L.jo_create.argtypes = [_dp, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_int]
@@ -69,8 +78,8 @@ def _d(a):
 class OracleEnv:
     """One reference-semantics environment on the CPU (JacoMujocoEnv restated)."""
 
-    def __init__(self, task="picking", variant="base", obs_mode=1, seed=0, env_id=0, f32=False, blob=None):
-        self.L = lib(f32)
+    def __init__(self, task="picking", variant="base", obs_mode=1, seed=0, env_id=0, f32=False, blob=None, fast=False):
+        self.L = lib(f32, fast)
         self.blob = load_blob() if blob is None else blob
         v = VARIANTS[variant] | (obs_mode << 4)
         self.h = self.L.jo_create(_d(self.blob), len(self.blob), TASKS[task], v, seed, env_id)

@@ -25,7 +25,7 @@ def _worker(rank, world, port, n_per_rank, outdir):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     from hostsim import HostSim
-    from mujoco_jaco_b200.shard import max_over_ranks, reduce_stats, shard_range
+    from mujoco_jaco_b200.shard import gather_per_rank, max_over_ranks, reduce_stats, shard_range
     off, n = shard_range(rank, world, n_per_rank)
     sim = HostSim(n, task="picking", seed=11, env_offset=off)
     obs0 = sim.reset()
@@ -35,8 +35,9 @@ def _worker(rank, world, port, n_per_rank, outdir):
     local_steps = float(stats[7])
     reduce_stats(stats)
     tmax = max_over_ranks(10.0 + rank)
+    table = gather_per_rank(torch.tensor([10.0 + rank, float(rank)]))      # bench.py's per-rank table
     np.savez(os.path.join(outdir, f"r{rank}.npz"), obs0=obs0, obs1=obs1, rew=rew, stats=stats.numpy(),
-             local_steps=local_steps, tmax=tmax)
+             local_steps=local_steps, tmax=tmax, table=np.array(table))
     dist.destroy_process_group()
 
 
@@ -56,6 +57,7 @@ def test_two_rank_shards_match_single_process(tmp_path):
         assert z["local_steps"] == n
         assert np.allclose(z["stats"], ref.stats)                         # all-reduced statistics == global run
         assert z["tmax"] == 11.0
+        assert np.array_equal(z["table"], [[10.0, 0.0], [11.0, 1.0]])
 
 
 def test_shard_range_validation():
