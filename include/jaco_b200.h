@@ -54,6 +54,18 @@ int jaco_reset(jaco_handle h, const uint8_t* mask, float* obs, void* stream);
 int jaco_step(jaco_handle h, const float* action, float* obs, float* reward, uint8_t* done, uint8_t* succ,
               float* wb, float* term_obs, int auto_reset, void* stream);
 
+/* jaco_step without any allocation.  NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same inputs, outputs
+ * and kernels as jaco_step (bit-identical results); the step kernels' scratch (work lists + counters) lives in a file-scope
+ * `static __device__` array of the library instead of the handle's cudaMalloc'ed buffers, resolved once per device at set-up
+ * (jaco_create) with cudaGetSymbolAddress.  Limits: n_envs <= JACO_NOALLOC_MAX_ENVS = 16384 (larger handles are rejected with
+ * JACO_EINVAL and a message in jaco_last_error); every GPU that loads the library holds the 128.25 KB array until exit; all calls on
+ * a device share it, so calls that overlap on the GPU (different streams / handles) race -- serialise them.  The entry point calls
+ * no cudaMalloc / cudaFree or allocating library routine; the handle itself (state, statistics) is allocated by jaco_create. */
+#define JACO_NOALLOC_MAX_ENVS 16384
+int jaco_step_noalloc(jaco_handle h, const float* action, float* obs, float* reward, uint8_t* done, uint8_t* succ,
+                      float* wb, float* term_obs, int auto_reset, void* stream);
+
 /* Same call with HOST buffers (the reference-facing path: numpy in, numpy out).  Copies the action to the
  * device, steps, copies the results back and synchronises the stream before returning. */
 int jaco_step_host(jaco_handle h, const float* action, float* obs, float* reward, uint8_t* done, uint8_t* succ,

@@ -22,7 +22,7 @@ SOURCES = [os.path.join(CSRC, u) for u in UNITS] + HEADERS
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-prec-div=false", "-prec-sqrt=true",
               "-ftz=true", "-Xcompiler", "-fPIC"]
 
-SYMBOLS = ["jaco_create", "jaco_destroy", "jaco_last_error", "jaco_reset", "jaco_step", "jaco_step_host",
+SYMBOLS = ["jaco_create", "jaco_destroy", "jaco_last_error", "jaco_reset", "jaco_step", "jaco_step_noalloc", "jaco_step_host",
            "jaco_get_state", "jaco_set_state", "jaco_debug_substep", "jaco_stats", "jaco_debug_counters", "jaco_n_envs",
            "jaco_launch_count", "jaco_fp32_peak_tflops"]
 
@@ -82,6 +82,7 @@ def load(path=None):
     L.jaco_last_error.restype = C.c_char_p
     L.jaco_reset.argtypes = [vp, vp, vp, vp]
     L.jaco_step.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, C.c_int, vp]
+    L.jaco_step_noalloc.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, C.c_int, vp]
     L.jaco_step_host.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int, vp]
     L.jaco_get_state.argtypes = [vp, vp, vp, vp, vp]
     L.jaco_set_state.argtypes = [vp, vp, vp, vp, vp]

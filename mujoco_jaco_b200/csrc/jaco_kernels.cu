@@ -28,6 +28,24 @@ struct jaco_sim_handle {
 };
 static jaco_sim_handle* g_model_owner = nullptr;   // handle whose model the __constant__ / __device__ symbols hold
 
+// ---- scratch of jaco_step_noalloc (include/jaco_b200.h): the step kernels' work lists and counters in a file-scope device array
+// instead of cudaMalloc'ed buffers.  Every GPU that loads the library holds these 128.25 KB until exit.  Layout (ints):
+// [0, 2 * MAX) work lists (row 0 general-path fall-backs, row 1 general resets; row stride = the handle's n_envs), then 64 counters.
+/* JACO_NOALLOC_MAX_ENVS (16384) comes from include/jaco_b200.h */
+#define JACO_NOALLOC_MAX_DEVICES 64
+static __device__ __align__(256) int g_noalloc_scratch[2 * JACO_NOALLOC_MAX_ENVS + 64];
+// In host code `g_noalloc_scratch` is a host-side stand-in, not a device address: the address a kernel may use is resolved once per
+// device, with that device current, by cudaGetSymbolAddress (at set-up: jaco_create) and cached here.
+static int* g_noalloc_ptr[JACO_NOALLOC_MAX_DEVICES];
+static cudaError_t noalloc_resolve(int device) {
+  if (device < 0 || device >= JACO_NOALLOC_MAX_DEVICES) return cudaErrorInvalidDevice;
+  if (g_noalloc_ptr[device]) return cudaSuccess;
+  void* p = nullptr;
+  cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);   // `device` is current (jaco_create has just set it)
+  if (e == cudaSuccess) g_noalloc_ptr[device] = static_cast<int*>(p);
+  return e;
+}
+
 __global__ void __launch_bounds__(JACO_BLOCK) jaco_reset_kernel(JacoCfg cfg, float* state, int N, int env_offset, const unsigned char* mask, float* obs) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= N) return;
@@ -152,6 +170,7 @@ int jaco_create(const void* model_blob, size_t nbytes, int n_envs, int task_id, 
   h->cfg.task = task_id; h->cfg.variant = variant & 15; h->cfg.obs_mode = (variant >> 4) & 15; h->cfg.seed = seed;
   h->cfg.task_max_steps = (task_id == JACO_REACHING || task_id == JACO_GRASPING) ? 500 : ((task_id == JACO_PICKING || task_id == JACO_PLACING) ? 700 : 1200);
   CK(cudaSetDevice(device));
+  CK(noalloc_resolve(device));   /* set-up for jaco_step_noalloc: device address of its static scratch, once per device */
   h->model = new JacoModel();
   jaco_model_from_blob((const double*)model_blob, h->model);
   CK(upload_model(h));
@@ -218,6 +237,33 @@ int jaco_step(jaco_handle h, const float* action, float* obs, float* reward, uin
     jaco_step_kernel<<<nblocks(h->n), JACO_BLOCK, 0, st>>>(h->cfg, h->state, h->n, h->env_offset, action, obs, reward, done, succ, wb, term_obs, auto_reset, h->stats);
     h->launches++;
   }
+  CK(cudaGetLastError());
+  return JACO_OK;
+}
+
+// jaco_step with its scratch (work lists, counters) in the library's static device array: allocates nothing.  Same kernels, same
+// arguments otherwise, so the outputs are bit-identical to jaco_step's.  All calls (all handles of a device) share the array: calls
+// that overlap on the GPU race.
+int jaco_step_noalloc(jaco_handle h, const float* action, float* obs, float* reward, uint8_t* done, uint8_t* succ, float* wb, float* term_obs, int auto_reset, void* stream) {
+  if (!h || !action || !obs || !reward || !done || !succ || !wb) return JACO_EINVAL;
+  if (h->n > JACO_NOALLOC_MAX_ENVS) {
+    snprintf(h->err, sizeof h->err, "jaco_step_noalloc: %d envs exceed the static scratch (JACO_NOALLOC_MAX_ENVS = %d); use jaco_step", h->n, JACO_NOALLOC_MAX_ENVS);
+    return JACO_EINVAL;
+  }
+  if (h->use_fast != 2) { snprintf(h->err, sizeof h->err, "jaco_step_noalloc: this model runs the general kernel, which has no scratch; use jaco_step"); return JACO_EINVAL; }
+  int* scratch = (h->device >= 0 && h->device < JACO_NOALLOC_MAX_DEVICES) ? g_noalloc_ptr[h->device] : nullptr;
+  if (!scratch) { snprintf(h->err, sizeof h->err, "jaco_step_noalloc: static scratch not resolved on device %d", h->device); return JACO_ECUDA; }
+  cudaStream_t st = (cudaStream_t)stream;
+  CK(upload_model(h));
+  int* worklist = scratch;                                  // [2][h->n]
+  int* counters = scratch + 2 * JACO_NOALLOC_MAX_ENVS;      // [16] of 64
+  JacoStepArgs A = {h->cfg, h->state, h->n, h->env_offset, action, obs, reward, done, succ, wb, term_obs, auto_reset, h->stats, worklist, counters};
+  const int nlist = (h->n + JACO_LIST_BLOCK - 1) / JACO_LIST_BLOCK;
+  CK(cudaMemsetAsync(counters, 0, 16 * sizeof(int), st));   // the array keeps the last call's contents: the list lengths must start at zero
+  CK(jaco_coop_launch(A, st));
+  jaco_step_list_kernel<<<nlist, JACO_LIST_BLOCK, 0, st>>>(h->cfg, h->state, nullptr, h->n, h->env_offset, action, obs, reward, done, succ, wb,
+                                                         term_obs, auto_reset, h->stats, worklist, counters);
+  h->launches += 2;
   CK(cudaGetLastError());
   return JACO_OK;
 }
