@@ -9,7 +9,9 @@
 2. reference_rest_heights.npz -- object rest heights from the grasping recordings (weak invariants).
 3. oracle_picking_rollout.npz -- oracle-generated regression vectors (seeded actions -> obs/reward/done) so a
    change of the oracle itself is detected; NOT evidence of agreement with MuJoCo.
-4. policy_*.npz -- HPC primitive policy known-answer vectors (see make_policy_golden in this file).
+4. reference_trajectory_sample.npz -- the first three episodes of the reference's grasping_trajectory_expert5.npz, verbatim keys and
+   dtypes: the on-disk format mujoco_jaco_b200/formats.py reads and writes.
+(policy_picking.npz: tests/golden/make_policy_golden.py; contact_snapshots.npz: tests/golden/make_contact_snapshots.py.)
 """
 import os
 import sys
@@ -37,6 +39,12 @@ def make_reference_fixtures():
              floor_rest_z=obs[8:12, 10].astype(np.float32))
 
 
+def make_trajectory_sample():
+    g = np.load(os.path.join(REF, "models_baseline/trajectories/grasping_trajectory_expert5.npz"), allow_pickle=True)
+    end = int(np.where(g["episode_starts"])[0][3])
+    np.savez_compressed(os.path.join(HERE, "reference_trajectory_sample.npz"), **{k: (g[k][:3] if k == "episode_returns" else g[k][:end]) for k in g.files})
+
+
 def make_oracle_rollout():
     from oracle.oracle import OracleEnv
     n, steps = 16, 4
@@ -55,5 +63,6 @@ def make_oracle_rollout():
 
 if __name__ == "__main__":
     make_reference_fixtures()
+    make_trajectory_sample()
     make_oracle_rollout()
     print("golden fixtures written to", HERE)
