@@ -37,7 +37,7 @@ struct JacoModel {
   float mass[JACO_NBODY], com[JACO_NBODY][3], inertia[JACO_NBODY][6];  // body frame, about COM: xx yy zz xy xz yz
   float free_qpos0[2][7];
   float motor_fr[6][2], finger_act[3][5];
-  float ee_off[3], ee_obj_off[3], base_pos[3], base_link_pos[3];
+  float ee_off[3], ee_obj_off[3], base_pos[3], base_link_pos[3], base_link_eul[3];
   float dof_invw[JACO_NV], meaninertia, hand_sphere[4];
   float body_sphere[4][4];  // bounding spheres (body frame: centre xyz, radius) of the collision geoms on bodies 6..9
   float dt, gravz;
@@ -76,7 +76,7 @@ static inline void jaco_model_from_blob(const double* b, JacoModel* m) {
   for (int i = 0; i < 3; i++) for (int j = 0; j < 5; j++) m->finger_act[i][j] = (float)b[JM_FINGER_ACT + 5 * i + j];
   for (int i = 0; i < 3; i++) {
     m->ee_off[i] = (float)b[JM_EE_OFFSET + i]; m->ee_obj_off[i] = (float)b[JM_EE_OBJ_OFFSET + i];
-    m->base_pos[i] = (float)b[JM_BASE_POSITION + i]; m->base_link_pos[i] = (float)b[JM_BASE_LINK_POSITION + i];
+    m->base_pos[i] = (float)b[JM_BASE_POSITION + i]; m->base_link_pos[i] = (float)b[JM_BASE_LINK_POSITION + i]; m->base_link_eul[i] = (float)b[JM_BASE_LINK_EULER + i];
   }
   for (int i = 0; i < JACO_NV; i++) m->dof_invw[i] = (float)b[JM_DOF_INVWEIGHT0 + i];
   m->meaninertia = (float)b[JM_MEANINERTIA];

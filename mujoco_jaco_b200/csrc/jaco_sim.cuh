@@ -32,6 +32,7 @@ static JacoModel g_jaco_model_host;
 
 #define JPI 3.14159265358979323846f
 #define JMINVAL 1e-15f
+#define JACO_GRASP_RESET_MAX 4000     // bound (substeps) of each of the reference's two unbounded grasping-reset servo loops (util:135-167)
 #ifndef JACO_SOLVER_MAXIT
 #define JACO_SOLVER_MAXIT 16           // Newton iterations per component (fast path / cooperative path).  Round 1 used 8: on the in-contact
                                        // snapshots 23 % of the cooperative solves then stopped on the cap and 3 of 4096 env steps flipped touch / success
@@ -1391,10 +1392,40 @@ JHD void rulebased_subgoal(const JacoCfg& cfg, S& s, int env_id, float* pos, flo
   rr[0] -= JPI / 2;
   for (int i = 0; i < 3; i++) ori[i] = rr[i] + (uni(cfg, s, env_id, 1, 3 + i) - 0.5f) / 10;
 }
+// env_mujoco_util_trans.py:848-862: global_to_local(prop) = (Rx Ry Rz)^T (prop - base_position), applied as written to positions and
+// to Euler triples alike; local_to_global(prop) = (Rx Ry Rz) prop + base_position
+JHD void global_to_local(const float* prop, float* out) {
+  float d[3]; v3sub(d, prop, MDL.base_link_pos);
+  get_rotation(out, MDL.base_link_eul[0], MDL.base_link_eul[1], MDL.base_link_eul[2], d, 1);
+}
+JHD void local_to_global(const float* prop, float* out) {
+  float r[3]; get_rotation(r, MDL.base_link_eul[0], MDL.base_link_eul[1], MDL.base_link_eul[2], prop, 0);
+  v3add(out, r, MDL.base_link_pos);
+}
 template <class S>
 JHD void get_observation(const JacoCfg& cfg, S& s, int env_id, float* o) {  // util:223-271
   get_gripper_pose(s);
   s.touch_index = get_touch(s);
+  // _cis / _trans _get_touch (env_mujoco_util_cis.py:568-578) tests "inner touch" with a second `if`, not `elif`: the grasp class 3 is
+  // always overwritten by 1 (thumb / index / pinky pads are inner pads).  Reproduced, not normalised: observation, reward (+0.75 for
+  // class 1 instead of +2.5 for class 3) and the success test (touch in {1, 3}) then match what the reference computes.
+  if (cfg.variant != 0 && s.touch_index == 3) s.touch_index = 1;
+  if (cfg.variant == 2 && cfg.obs_mode == 1) {   // env_mujoco_util_trans.py:295-313
+    float sp[3], so[3], t[3];
+    const float zero[3] = {0, 0, 0}, dori[3] = {0, JPI / 2, 0};
+    o[0] = (float)s.touch_index;
+    global_to_local(s.gripper_pose, o + 1);
+    global_to_local(s.gripper_pose + 3, t); for (int i = 0; i < 3; i++) o[4 + i] = t[i] / JPI;
+    o[7] = (s.grip - 0.8f) / 0.2f;
+    global_to_local(obj_pos(s), o + 8);
+    global_to_local(zero, o + 11);
+    global_to_local(s.dest_goal, o + 14);
+    rulebased_subgoal(cfg, s, env_id, sp, so);
+    global_to_local(sp, o + 17);
+    global_to_local(so, t); for (int i = 0; i < 3; i++) o[20 + i] = t[i] / JPI;
+    global_to_local(dori, o + 23);
+    return;
+  }
   float sp[3], so[3], base[3] = {0, 0, 0};
   if (cfg.variant != 0) v3copy(base, MDL.base_link_pos);
   o[0] = (float)s.touch_index;
@@ -1560,7 +1591,8 @@ JHD void reset_sample(const JacoCfg& cfg, S& s, int env_id) {
   s.reach_goal[3] = round_half(alpha); s.reach_goal[4] = round_half(beta); s.reach_goal[5] = round_half(gamma);
   s.obj_goal[0] = uniab(cfg, s, env_id, 0, 13, -0.1f, 0.1f); s.obj_goal[1] = 0.65f + uniab(cfg, s, env_id, 0, 14, -0.08f, 0.02f); s.obj_goal[2] = 0.1898f;
   s.dest_goal[0] = 0.4f + uniab(cfg, s, env_id, 0, 15, -0.05f, 0.05f); s.dest_goal[1] = 0.3f + uniab(cfg, s, env_id, 0, 16, -0.05f, 0.05f); s.dest_goal[2] = 0.3468f;
-  if (cfg.variant != 0) for (int i = 0; i < 3; i++) { s.obj_goal[i] += m.base_link_pos[i]; s.dest_goal[i] += m.base_link_pos[i]; }
+  if (cfg.variant == 2) { float g[3]; local_to_global(s.obj_goal, g); v3copy(s.obj_goal, g); local_to_global(s.dest_goal, g); v3copy(s.dest_goal, g); }   // trans:265-270
+  else if (cfg.variant != 0) for (int i = 0; i < 3; i++) { s.obj_goal[i] += m.base_link_pos[i]; s.dest_goal[i] += m.base_link_pos[i]; }
   if (cfg.variant == 0) { s.qpos[16] = s.dest_goal[0]; s.qpos[17] = s.dest_goal[1]; for (int i = 16; i < JACO_NV; i++) s.qvel[i] = 0; }
 }
 // env_mujoco.py:99-102 -> util:92-174.  Leaves mjData (the JacoSim working set) evaluated at the reset state.
@@ -1592,6 +1624,37 @@ JHD void env_reset(const JacoCfg& cfg, JacoSim& s, int env_id, float* obs) {
     mj_forward(s, true);
   }
   if (cfg.task == JACO_TASK_REACHING) { for (int i = 0; i < 6; i++) s.target[i] = s.reach_goal[i]; }
+  else if (cfg.task == JACO_TASK_GRASPING) {
+    // util:123-167: two approach servo loops.  Unbounded `while True` in the reference; bounded here (JACO_GRASP_RESET_MAX substeps
+    // each: 4 s of simulated time, the approach takes ~0.5-1.5 s at the controller's 0.4 m/s limit).
+    get_gripper_pose(s);
+    float d[3], u[6]; v3sub(d, s.obj_goal, s.gripper_pose);
+    const float sx = d[0] > 0 ? 1.0f : (d[0] < 0 ? -1.0f : 0.0f);
+    float ori[3] = {round_half(-asinf(d[1] / sqrtf(d[1] * d[1] + d[2] * d[2])) * sx), round_half(acosf(d[0] / v3norm(d)) * sx),
+                    round_half(uniab(cfg, s, env_id, 0, 17, -0.1f, 0.1f))};
+    for (int i = 0; i < 3; i++) { s.target[i] = s.obj_goal[i]; s.target[3 + i] = ori[i]; }
+    float qt[4]; euler_rxyz_to_quat(qt, s.reach_goal[3], s.reach_goal[4], s.reach_goal[5]); quat_normalize(qt);
+    for (int it = 0; it < JACO_GRASP_RESET_MAX; it++) {
+      for (int i = 9; i < JACO_NV; i++) s.qvel[i] = 0;   // stop_obj (mujoco.py:239-246), then sim.forward()
+      mj_forward(s, false);
+      osc_generate(s, s.qvel, u);
+      substep(s, u, 0, true);
+      get_gripper_pose(s);
+      v3sub(d, s.gripper_pose, s.obj_goal);
+      float qg[4]; euler_rxyz_to_quat(qg, s.gripper_pose[3], s.gripper_pose[4], s.gripper_pose[5]); quat_normalize(qg);
+      float ad = 0; for (int i = 0; i < 4; i++) ad += (qg[i] - qt[i]) * (qg[i] - qt[i]);
+      if (v3norm(d) < 0.2f) { for (int i = 0; i < 3; i++) s.target[i] = s.gripper_pose[i]; break; }
+      if (sqrtf(ad) < JPI / 6) break;
+    }
+    for (int it = 0; it < JACO_GRASP_RESET_MAX; it++) {
+      osc_generate(s, s.qvel, u);
+      substep(s, u, 0, true);
+      get_gripper_pose(s);
+      for (int i = 0; i < 3; i++) s.target[i] = s.obj_goal[i];
+      v3sub(d, s.gripper_pose, s.obj_goal);
+      if (v3norm(d) < 0.15f) break;
+    }
+  }
   else if (cfg.task != JACO_TASK_PLACING) { get_gripper_pose(s); for (int i = 0; i < 6; i++) s.target[i] = s.gripper_pose[i]; }
   get_observation(cfg, s, env_id, obs);
   s.rng_counter += 1;

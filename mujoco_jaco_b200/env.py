@@ -40,7 +40,7 @@ class JacoVecEnv:
     """Batched Jaco environment on one GPU (one independent shard of the global env range)."""
 
     def __init__(self, n_envs, task="picking", variant="base", obs_mode=1, seed=0, device=0, env_offset=0,
-                 robot_file="jaco2_curtain_torque", auto_reset=True):
+                 robot_file="jaco2_curtain_torque", auto_reset=True, model_blob=None):
         if not torch.cuda.is_available():
             raise RuntimeError("JacoVecEnv needs a CUDA device: mujoco_jaco_b200 has no CPU fallback")
         if task not in TASKS:
@@ -48,7 +48,8 @@ class JacoVecEnv:
         self.L = _lib.load()
         self.n_envs, self.task, self.auto_reset = int(n_envs), task, auto_reset
         self.device = torch.device("cuda", device)
-        blob = load_model_blob(robot_file)
+        # model_blob: a compiled model other than the shipped one (layout of include/jaco_model_layout.h), e.g. another base pose
+        blob = load_model_blob(robot_file) if model_blob is None else np.ascontiguousarray(model_blob, np.float64)
         h = C.c_void_p()
         rc = self.L.jaco_create(blob.ctypes.data_as(C.c_void_p), blob.nbytes, self.n_envs, TASKS[task],
                                 VARIANTS[variant] | (obs_mode << 4), device, seed, env_offset, C.byref(h))
@@ -176,7 +177,10 @@ class JacoMujocoEnv:
         robot_file = kwargs.get("robot_file", "jaco2_curtain_torque") or "jaco2_curtain_torque"
         self.task = kwargs.get("task", None)
         obs_mode = 2 if kwargs.get("subgoal_obs", False) else (1 if kwargs.get("rulebased_subgoal", False) else 0)
-        seed = kwargs.get("seed", 0) or 0
+        # the reference draws from unseeded np.random (every worker process its own episodes): without an explicit seed take one from the OS
+        seed = kwargs.get("seed", None)
+        if seed is None:
+            seed = int.from_bytes(os.urandom(4), "little")
         self._vec = JacoVecEnv(1, task=self.task, variant=kwargs.get("variant", "base"), obs_mode=obs_mode, seed=int(seed),
                                device=kwargs.get("device", 0), robot_file=robot_file, auto_reset=False)
         self.current_steps, self.max_steps = 0, 2500

@@ -223,6 +223,9 @@ def compile_model(xml_path):
     A["ee_obj_offset"] = rel_frame(model, model.body_id("EE_obj"), link6)[0]
     A["base_position"] = rel_frame(model, model.body_id("link1"), 0)[0]          # env_mujoco_util.py:35
     A["base_link_position"] = rel_frame(model, model.body_id("base_link"), 0)[0]  # _cis variant :42
+    # _trans variant (env_mujoco_util_trans.py:43): base_link orientation as Gohlke 'rxyz' Euler angles, R = Rx(a) Ry(b) Rz(c)
+    Rb = quat_to_mat(rel_frame(model, model.body_id("base_link"), 0)[1])
+    A["base_link_euler"] = np.array([np.arctan2(-Rb[1, 2], Rb[2, 2]), np.arcsin(np.clip(Rb[0, 2], -1, 1)), np.arctan2(-Rb[0, 1], Rb[0, 0])])
 
     # ---- unmerged tree at qpos0: M, invweight0 (mj_setConst semantics) ---------------------------------
     nv = 21

@@ -18,6 +18,7 @@ typedef double real;
 #define rcos(x) ((real)cos((double)(x)))
 #define ratan2(y, x) ((real)atan2((double)(y), (double)(x)))
 #define racos(x) ((real)acos((double)(x)))
+#define rasin(x) ((real)asin((double)(x)))
 #define rexp(x) ((real)exp((double)(x)))
 #define rpow(x, y) ((real)pow((double)(x), (double)(y)))
 #define rabs(x) ((real)fabs((double)(x)))
@@ -165,7 +166,7 @@ struct jo_env {
   real mass[NB], com[NB][3], inertia[NB][9]; /* body-frame, index by body id (0 world unused) */
   real free_qpos0[2][7];
   real motor_fr[6][2], finger_act[3][5];
-  real ee_off[3], ee_obj_off[3], base_pos[3], base_link_pos[3];
+  real ee_off[3], ee_obj_off[3], base_pos[3], base_link_pos[3], base_link_eul[3];
   real dof_invw[NV], meaninertia, hand_sphere[4];
   real dt, gravz, tol; int maxiter;
   geom_t geoms[JM_NGEOM]; pair_t pairs[JM_NPAIR]; site_t sites[JM_NSITE];
@@ -212,7 +213,7 @@ static void load_model(jo_env *e, const double *b) {
   }
   for (int i = 0; i < 6; i++) { e->motor_fr[i][0] = R_(b[JM_MOTOR_FORCERANGE + 2 * i]); e->motor_fr[i][1] = R_(b[JM_MOTOR_FORCERANGE + 2 * i + 1]); }
   for (int i = 0; i < 3; i++) for (int j = 0; j < 5; j++) e->finger_act[i][j] = R_(b[JM_FINGER_ACT + 5 * i + j]);
-  for (int i = 0; i < 3; i++) { e->ee_off[i] = R_(b[JM_EE_OFFSET + i]); e->ee_obj_off[i] = R_(b[JM_EE_OBJ_OFFSET + i]); e->base_pos[i] = R_(b[JM_BASE_POSITION + i]); e->base_link_pos[i] = R_(b[JM_BASE_LINK_POSITION + i]); }
+  for (int i = 0; i < 3; i++) { e->ee_off[i] = R_(b[JM_EE_OFFSET + i]); e->ee_obj_off[i] = R_(b[JM_EE_OBJ_OFFSET + i]); e->base_pos[i] = R_(b[JM_BASE_POSITION + i]); e->base_link_pos[i] = R_(b[JM_BASE_LINK_POSITION + i]); e->base_link_eul[i] = R_(b[JM_BASE_LINK_EULER + i]); }
   for (int i = 0; i < NV; i++) e->dof_invw[i] = R_(b[JM_DOF_INVWEIGHT0 + i]);
   e->meaninertia = R_(b[JM_MEANINERTIA]);
   for (int i = 0; i < 4; i++) e->hand_sphere[i] = R_(b[JM_HAND_SPHERE + i]);
@@ -947,9 +948,40 @@ static void rulebased_subgoal(jo_env *e, real *pos, real *ori) { /* util:273-300
   rr[0] -= PI_ / 2;
   for (int i = 0; i < 3; i++) ori[i] = rr[i] + (uni(e, 1, 3 + i) - R_(0.5)) / 10;
 }
+/* env_mujoco_util_trans.py:848-854: global_to_local(prop) = (Rx Ry Rz)^T (prop - base_position), applied AS WRITTEN to positions and to
+   Euler triples alike (the 'orientation' branch is the same expression: an Euler triple minus the base translation, rotated) */
+static void global_to_local(const jo_env *e, const real *prop, real *out) {
+  real d[3]; v3sub(d, prop, e->base_link_pos);
+  get_rotation(out, e->base_link_eul[0], e->base_link_eul[1], e->base_link_eul[2], d, 1);
+}
+/* env_mujoco_util_trans.py:856-862: local_to_global(prop) = (Rx Ry Rz) prop + base_position */
+static void local_to_global(const jo_env *e, const real *prop, real *out) {
+  real r[3]; get_rotation(r, e->base_link_eul[0], e->base_link_eul[1], e->base_link_eul[2], prop, 0);
+  v3add(out, r, e->base_link_pos);
+}
+static void get_observation_trans(jo_env *e, float *obs) { /* env_mujoco_util_trans.py:295-313 (rulebased_subgoal branch) */
+  real o[JO_OBS], sp[3], so[3], t[3];
+  const real zero[3] = {0, 0, 0}, dori[3] = {0, PI_ / 2, 0};
+  o[0] = (real)e->touch_index;
+  global_to_local(e, e->gripper_pose, o + 1);
+  global_to_local(e, e->gripper_pose + 3, t); for (int i = 0; i < 3; i++) o[4 + i] = t[i] / PI_;
+  o[7] = (e->gripper_angle - R_(0.8)) / R_(0.2);
+  global_to_local(e, e->obj_xpos, o + 8);
+  global_to_local(e, zero, o + 11);
+  global_to_local(e, e->dest_goal, o + 14);
+  rulebased_subgoal(e, sp, so);
+  global_to_local(e, sp, o + 17);
+  global_to_local(e, so, t); for (int i = 0; i < 3; i++) o[20 + i] = t[i] / PI_;
+  global_to_local(e, dori, o + 23);
+  for (int i = 0; i < JO_OBS; i++) obs[i] = (float)o[i];
+}
 static void get_observation(jo_env *e, float *obs) { /* util:223-271 (+ _cis :267-328, _trans :274-) */
   get_gripper_pose(e);
   e->touch_index = get_touch(e);
+  /* env_mujoco_util_cis.py:568-578: the variants' _get_touch uses `if` (not `elif`) for the inner-touch test, so the grasp class 3 is
+     always overwritten by 1.  Reproduced as written. */
+  if (e->variant != JO_VAR_BASE && e->touch_index == 3) e->touch_index = 1;
+  if (e->variant == JO_VAR_TRANS && e->obs_mode == 1) { get_observation_trans(e, obs); return; }
   real o[JO_OBS], sp[3], so[3], base[3] = {0, 0, 0};
   if (e->variant != JO_VAR_BASE) v3copy(base, e->base_link_pos);
   o[0] = (real)e->touch_index;
@@ -1112,7 +1144,8 @@ void jo_reset(jo_env *e, float *obs) { /* env_mujoco.py:99-102 -> util:92-174 */
       e->reach_goal[3 + i] = R_(v); } }
   e->obj_goal[0] = uniab(e, 0, 13, -0.1, 0.1); e->obj_goal[1] = R_(0.65) + uniab(e, 0, 14, -0.08, 0.02); e->obj_goal[2] = R_(0.1898);
   e->dest_goal[0] = R_(0.4) + uniab(e, 0, 15, -0.05, 0.05); e->dest_goal[1] = R_(0.3) + uniab(e, 0, 16, -0.05, 0.05); e->dest_goal[2] = R_(0.3468);
-  if (e->variant != JO_VAR_BASE) for (int i = 0; i < 3; i++) { e->obj_goal[i] += e->base_link_pos[i]; e->dest_goal[i] += e->base_link_pos[i]; }
+  if (e->variant == JO_VAR_TRANS) { real g[3]; local_to_global(e, e->obj_goal, g); v3copy(e->obj_goal, g); local_to_global(e, e->dest_goal, g); v3copy(e->dest_goal, g); } /* trans:265-270 */
+  else if (e->variant != JO_VAR_BASE) for (int i = 0; i < 3; i++) { e->obj_goal[i] += e->base_link_pos[i]; e->dest_goal[i] += e->base_link_pos[i]; }
   if (e->variant == JO_VAR_BASE) { /* set_dest_xyz, mujoco.py:229-237 (qvel[16:] quirk kept) */
     e->qpos[16] = e->dest_goal[0]; e->qpos[17] = e->dest_goal[1];
     for (int i = 16; i < NV; i++) e->qvel[i] = 0;
@@ -1134,6 +1167,35 @@ void jo_reset(jo_env *e, float *obs) { /* env_mujoco.py:99-102 -> util:92-174 */
     set_obj(e, e->obj_goal, zq);
   }
   if (e->task == JO_TASK_REACHING) memcpy(e->target, e->reach_goal, sizeof e->target);
+  else if (e->task == JO_TASK_GRASPING) { /* util:123-167: two approach servo loops (unbounded in the reference; bounded here, JO_GRASP_RESET_MAX substeps each) */
+    get_gripper_pose(e);
+    real d[3]; v3sub(d, e->obj_goal, e->gripper_pose);
+    real sx = d[0] > 0 ? R_(1) : (d[0] < 0 ? R_(-1) : R_(0));
+    real ori[3] = {-rasin(d[1] / rsqrt_(d[1] * d[1] + d[2] * d[2])) * sx, racos(d[0] / v3norm(d)) * sx, uniab(e, 0, 17, -0.1, 0.1)};
+    for (int i = 0; i < 3; i++) { double v = (double)ori[i]; if (v != 0) { int ex; double m = frexp(v, &ex); m = nearbyint(m * 2048.0) / 2048.0; v = ldexp(m, ex); } ori[i] = R_(v); } /* dtype=np.float16 */
+    for (int i = 0; i < 3; i++) { e->target[i] = e->obj_goal[i]; e->target[3 + i] = ori[i]; }
+    real qt[4]; euler_rxyz_to_quat(qt, e->reach_goal[3], e->reach_goal[4], e->reach_goal[5]);
+    { real n = rsqrt_(qt[0] * qt[0] + qt[1] * qt[1] + qt[2] * qt[2] + qt[3] * qt[3]); for (int i = 0; i < 4; i++) qt[i] /= n; }
+    for (int it = 0; it < JO_GRASP_RESET_MAX; it++) {
+      for (int i = 9; i < NV; i++) e->qvel[i] = 0; /* stop_obj (mujoco.py:239-246) */
+      mj_forward(e);
+      step_simulation(e);
+      get_gripper_pose(e);
+      v3sub(d, e->gripper_pose, e->obj_goal);
+      real qg[4]; euler_rxyz_to_quat(qg, e->gripper_pose[3], e->gripper_pose[4], e->gripper_pose[5]);
+      { real n = rsqrt_(qg[0] * qg[0] + qg[1] * qg[1] + qg[2] * qg[2] + qg[3] * qg[3]); for (int i = 0; i < 4; i++) qg[i] /= n; }
+      real ad = 0; for (int i = 0; i < 4; i++) ad += (qg[i] - qt[i]) * (qg[i] - qt[i]);
+      if (v3norm(d) < R_(0.2)) { for (int i = 0; i < 3; i++) e->target[i] = e->gripper_pose[i]; break; }
+      if (rsqrt_(ad) < PI_ / 6) break;
+    }
+    for (int it = 0; it < JO_GRASP_RESET_MAX; it++) {
+      step_simulation(e);
+      get_gripper_pose(e);
+      for (int i = 0; i < 3; i++) e->target[i] = e->obj_goal[i];
+      v3sub(d, e->gripper_pose, e->obj_goal);
+      if (v3norm(d) < R_(0.15)) break;
+    }
+  }
   else if (e->task != JO_TASK_PLACING) { get_gripper_pose(e); memcpy(e->target, e->gripper_pose, sizeof e->target); } /* util:65 (ctor) */
   get_observation(e, obs);
   e->rng_counter += 1;

@@ -31,6 +31,7 @@ enum { JO_VAR_BASE = 0, JO_VAR_CIS = 1, JO_VAR_TRANS = 2 };
 #define JO_AUX 64
 #define JO_MAXCON 96
 #define JO_MAXEFC 1024
+#define JO_GRASP_RESET_MAX 4000 /* bound (substeps) of each of the reference's two unbounded grasping-reset servo loops (util:135-167) */
 
 typedef struct jo_env jo_env;
 

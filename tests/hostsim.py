@@ -32,6 +32,22 @@ def lib():
     return _lib
 
 
+def set_blob(blob=None):
+    """(re)initialise the harness' model from `blob` (None = the shipped model).  The model is a global of the harness library."""
+    L = lib()
+    if blob is None:
+        blob = np.load(os.path.join(REPO, "mujoco_jaco_b200", "model", "jaco2_curtain_torque.npz"))["blob"]
+    blob = np.ascontiguousarray(blob, np.float64)
+    L.hh_init(blob.ctypes.data_as(C.POINTER(C.c_double)))
+
+
+def layout_offsets():
+    """{name: offset} parsed from include/jaco_model_layout.h"""
+    import re
+    txt = open(os.path.join(REPO, "include", "jaco_model_layout.h")).read()
+    return {m.group(1): int(m.group(2)) for m in re.finditer(r"#define JM_([A-Z0-9_]+) (\d+)", txt)}
+
+
 def fp(a):
     return a.ctypes.data_as(_f)
 

@@ -24,20 +24,26 @@ def _close(a, b, rtol, atol):
     return np.abs(a - b) <= atol + rtol * np.abs(b)
 
 
-@pytest.mark.parametrize("task", ["picking", "reaching", "pickAndplace"])
+@pytest.mark.parametrize("task", ["picking", "reaching", "pickAndplace", "grasping"])
 def test_reset_matches_oracle(task):
     from mujoco_jaco_b200.env import JacoVecEnv
-    n = 256
+    n = 64 if task == "grasping" else 256
     env = JacoVecEnv(n, task=task, seed=5, auto_reset=False)
     obs = env.reset().cpu().numpy()
     q, v, aux = [t.cpu().numpy() for t in env.get_state()]
     ora = _oracles(task, 5, n)
     oobs = np.stack([o.reset() for o in ora])
-    assert np.abs(obs - oobs).max() < 5e-6
+    # grasping: two approach servo loops of ~1000 substeps precede the first observation (util:123-167)
+    tol = 5e-5 if task == "grasping" else 5e-6
+    assert np.abs(obs - oobs).max() < tol
     for i in (0, 17, n - 1):
         oq, ov, oa = ora[i].get_state()
-        assert np.abs(q[i] - oq).max() < 1e-6 and np.abs(v[i] - ov).max() < 1e-6
-        assert np.abs(aux[i, :64] - oa).max() < 1e-5
+        assert np.abs(q[i] - oq).max() < (5e-5 if task == "grasping" else 1e-6) and np.abs(v[i] - ov).max() < (1e-3 if task == "grasping" else 1e-6)
+        assert np.abs(aux[i, :23] - oa[:23]).max() < (5e-5 if task == "grasping" else 1e-5)
+        if task != "grasping":
+            assert np.abs(aux[i, :64] - oa).max() < 1e-5
+    if task == "grasping":
+        assert (np.linalg.norm(obs[:, 1:4] - aux[:, 11:14], axis=1) < 0.15 + 1e-3).all()
 
 
 def test_one_substep_state_and_contacts_picking():
