@@ -29,9 +29,11 @@ extern "C" {
 
 enum { JACO_OK = 0, JACO_EINVAL = -1, JACO_ECUDA = -2, JACO_ENOMEM = -3 };
 /* task ids: argparser.py --task */
-enum { JACO_REACHING = 0, JACO_GRASPING = 1, JACO_PICKING = 2, JACO_PLACING = 3, JACO_PICKANDPLACE = 4 };
-/* variant = observation variant (0 env_mujoco_util.py, 1 _cis, 2 _trans) | obs_mode << 4
- * obs_mode: 0 reaching goal (util:255-270), 1 rule-based subgoal (util:240-254, what main.py uses), 2 subgoal_obs */
+enum { JACO_REACHING = 0, JACO_GRASPING = 1, JACO_PICKING = 2, JACO_PLACING = 3, JACO_PICKANDPLACE = 4, JACO_RELEASING = 5, JACO_CARRYING = 6 };
+/* variant = observation variant (0 env_mujoco_util.py, 1 _cis, 2 _trans) | obs_mode << 4 | binary << 8
+ * obs_mode: 0 reaching goal (util:255-270), 1 rule-based subgoal (util:240-254, what main.py uses), 2 subgoal_obs
+ * binary: the _cis / _trans sparse picking reward (env_mujoco_util_cis.py:56,459,637-660: reward 0, +10 on success, -1 on a drop);
+ *         the reference never sets it (self.binary = False), it is reachable here for completeness */
 
 typedef struct jaco_sim_handle* jaco_handle;
 
@@ -86,6 +88,17 @@ int jaco_debug_substep(jaco_handle h, const float* ctrl, int32_t* ncon, float* s
  * {episodes, successes, return_sum, timeouts, drops, singular_exits, nan_resets, env_steps, length_sum, 0...}.
  * This is the vector the multi-GPU harness all-reduces (env_mujoco.py:129-135 success-rate log). */
 int jaco_stats(jaco_handle h, float* out16, int clear, void* stream);
+
+/* JacoMujocoEnvUtil._get_camera (util:302-307: offscreen.render(640, 480, camera_id=0) + read_pixels(depth=True), flipped top-down)
+ * for envs [env_begin, env_begin + env_count): a headless CUDA ray caster over the model's analytic primitives (the reference's
+ * OpenGL path is unavailable on this box; mujoco_jaco_b200/csrc/jaco_render.cuh says what is drawn).
+ * camera19 (host): pos[3], R[9] (row-major; columns = camera right / up / backward axes in the world, MuJoCo convention: the camera
+ * looks along its -z), fovy in degrees, znear, zfar (metres), ambient, 3 unused.  prim_rgb (host): float[JACO_RENDER_PRIMS][3].
+ * Outputs on the device: rgb uint8[env_count][height][width][3] (row 0 = top), depth float[env_count][height][width]
+ * (OpenGL-normalised like read_pixels: (1/znear - 1/z) / (1/znear - 1/zfar), 1.0 where nothing is hit). */
+#define JACO_RENDER_PRIMS 35
+int jaco_render(jaco_handle h, const float* camera19, const float* prim_rgb, int width, int height, int env_begin, int env_count,
+                uint8_t* rgb, float* depth, void* stream);
 
 /* diagnostics: host copy of the step work-list counters, out int32[16] = {n_bail, n_reset of the last step,
  * cumulative bail-reason histogram (limit, hand, forearm, object, dest, osc, nan), ...}; synchronises the device. */

@@ -11,7 +11,7 @@ SO_PATH = os.path.join(HERE, "libjaco_b200.so")
 CSRC = os.path.join(HERE, "csrc")
 UNITS = ["jaco_kernels.cu", "jaco_kernel_coop.cu"]            # compiled in parallel, linked into one .so
 DIAG_UNITS = []
-HEADERS = [os.path.join(CSRC, f) for f in ("jaco_sim.cuh", "jaco_fast.cuh", "jaco_coop.cuh", "jaco_launch.h", "jaco_model.h")] + [
+HEADERS = [os.path.join(CSRC, f) for f in ("jaco_sim.cuh", "jaco_fast.cuh", "jaco_coop.cuh", "jaco_launch.h", "jaco_model.h", "jaco_render.cuh")] + [
     os.path.join(REPO, "include", "jaco_b200.h"), os.path.join(REPO, "include", "jaco_model_layout.h")]
 SOURCES = [os.path.join(CSRC, u) for u in UNITS] + HEADERS
 # -prec-div=false -ftz=true: 2-ulp division and flushed denormals.  IEEE division expands to ~10-instruction sequences with
@@ -24,7 +24,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 
 SYMBOLS = ["jaco_create", "jaco_destroy", "jaco_last_error", "jaco_reset", "jaco_step", "jaco_step_noalloc", "jaco_step_host",
            "jaco_get_state", "jaco_set_state", "jaco_debug_substep", "jaco_stats", "jaco_debug_counters", "jaco_n_envs",
-           "jaco_launch_count", "jaco_fp32_peak_tflops"]
+           "jaco_launch_count", "jaco_fp32_peak_tflops", "jaco_render"]
 
 
 def needs_build():
@@ -92,6 +92,7 @@ def load(path=None):
     L.jaco_n_envs.argtypes = [vp]
     L.jaco_launch_count.argtypes = [vp]
     L.jaco_launch_count.restype = C.c_longlong
+    L.jaco_render.argtypes = [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp]
     L.jaco_fp32_peak_tflops.argtypes = [C.c_int, C.c_int]
     L.jaco_fp32_peak_tflops.restype = C.c_double
     _lib = L

@@ -1248,7 +1248,7 @@ JHD int step_end(const JacoCfg& cfg, FastSim& s, int env_id, float* obs, float* 
   s.current_steps += 1;
   if (s.current_steps < cfg.task_max_steps) d = terminal_inspection(cfg, s, &bonus, &w, &sc);
   else { d = 1; bonus = -10; w = 0; sc = 0; }
-  *cause = !d ? 0 : (sc ? 1 : (s.current_steps >= cfg.task_max_steps ? 2 : (bonus == -1.0f ? 3 : (bonus == -20.0f ? 4 : 5))));
+  *cause = !d ? 0 : (sc ? 1 : (s.current_steps >= cfg.task_max_steps ? 2 : (JPI - 0.1f < s.qpos[2] && s.qpos[2] < JPI + 0.1f ? 3 : (bonus < 0 ? 4 : 5))));
   r += bonus;
   if (!(r == r)) return 0;
   *reward = r; *done = d; *succ = sc; *wb = w;
@@ -1262,7 +1262,7 @@ JHD int step_end(const JacoCfg& cfg, FastSim& s, int env_id, float* obs, float* 
 // takes from that forward).  Returns 0 when the proximity tests cannot prove it: the caller hands the env to the
 // general reset kernel.
 JHD JNOINLINE int fast_reset(const JacoCfg& cfg, FastSim& s, int env_id, float* obs) {
-  if (cfg.task == JACO_TASK_PLACING || cfg.task == JACO_TASK_GRASPING) return 0;
+  if (cfg.task == JACO_TASK_PLACING || cfg.task == JACO_TASK_GRASPING || cfg.task == JACO_TASK_RELEASING || cfg.task == JACO_TASK_CARRYING) return 0;
   reset_sample(cfg, s, env_id);
   if (cfg.task != JACO_TASK_REACHING) {   // set_obj_xyz(obj_goal, [0,0,0,0]) (util:119-121, mujoco.py:217-227)
     for (int i = 0; i < 3; i++) s.qpos[9 + i] = s.obj_goal[i];

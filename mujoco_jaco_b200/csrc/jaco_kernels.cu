@@ -10,6 +10,7 @@
 #include <new>
 #include "../../include/jaco_b200.h"
 #include "jaco_launch.h"
+#include "jaco_render.cuh"
 
 #define JACO_BLOCK 128
 
@@ -24,6 +25,7 @@ struct jaco_sim_handle {
   int* counters;       // [16]: 0 n_fallback, 1 n_reset, 2..7 bail-reason histogram (cumulative, diagnostics)
   JacoModel* model;    // host copy: the model symbols are per library, a handle re-uploads them when another handle used them last
   long long launches;
+  float* render_prims; int render_cap;   // jaco_render scratch: world primitives of the rendered envs (grown on demand)
   char err[256];
 };
 static jaco_sim_handle* g_model_owner = nullptr;   // handle whose model the __constant__ / __device__ symbols hold
@@ -161,14 +163,14 @@ static cudaError_t upload_model(jaco_sim_handle* h) {
 extern "C" {
 
 int jaco_create(const void* model_blob, size_t nbytes, int n_envs, int task_id, int variant, int device, uint64_t seed, int env_offset, jaco_handle* out) {
-  if (!model_blob || !out || n_envs <= 0 || nbytes != sizeof(double) * JM_TOTAL || task_id < 0 || task_id > 4) return JACO_EINVAL;
+  if (!model_blob || !out || n_envs <= 0 || nbytes != sizeof(double) * JM_TOTAL || task_id < 0 || task_id > JACO_CARRYING) return JACO_EINVAL;
   jaco_sim_handle* h = new (std::nothrow) jaco_sim_handle();
   if (!h) return JACO_ENOMEM;
   memset(h, 0, sizeof *h);
   *out = h;
   h->n = n_envs; h->device = device; h->env_offset = env_offset;
-  h->cfg.task = task_id; h->cfg.variant = variant & 15; h->cfg.obs_mode = (variant >> 4) & 15; h->cfg.seed = seed;
-  h->cfg.task_max_steps = (task_id == JACO_REACHING || task_id == JACO_GRASPING) ? 500 : ((task_id == JACO_PICKING || task_id == JACO_PLACING) ? 700 : 1200);
+  h->cfg.task = task_id; h->cfg.variant = variant & 15; h->cfg.obs_mode = (variant >> 4) & 15; h->cfg.binary = (variant >> 8) & 1; h->cfg.seed = seed;
+  h->cfg.task_max_steps = (task_id == JACO_REACHING || task_id == JACO_GRASPING || task_id == JACO_RELEASING || task_id == JACO_CARRYING) ? 500 : ((task_id == JACO_PICKING || task_id == JACO_PLACING) ? 700 : 1200);
   CK(cudaSetDevice(device));
   CK(noalloc_resolve(device));   /* set-up for jaco_step_noalloc: device address of its static scratch, once per device */
   h->model = new JacoModel();
@@ -196,12 +198,43 @@ void jaco_destroy(jaco_handle h) {
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
   cudaFree(h->state); cudaFree(h->stats); cudaFree(h->worklist); cudaFree(h->counters);
+  cudaFree(h->render_prims);
   cudaFree(h->s_action); cudaFree(h->s_obs); cudaFree(h->s_reward); cudaFree(h->s_wb); cudaFree(h->s_done); cudaFree(h->s_succ);
   if (g_model_owner == h) g_model_owner = nullptr;
   delete h->model;
   delete h;
 }
 const char* jaco_last_error(jaco_handle h) { return h ? h->err : "null handle"; }
+
+int jaco_render(jaco_handle h, const float* camera19, const float* prim_rgb, int width, int height, int env_begin, int env_count,
+                uint8_t* rgb, float* depth, void* stream) {
+  if (!h || !camera19 || !prim_rgb || !rgb || !depth || width <= 0 || height <= 0 || env_begin < 0 || env_count <= 0 || env_begin + env_count > h->n ||
+      env_count > 65535) {
+    if (h) snprintf(h->err, sizeof h->err, "jaco_render: bad arguments (env range [%d, %d) of %d, %d x %d; at most 65535 envs per call)", env_begin, env_begin + env_count, h->n, width, height);
+    return JACO_EINVAL;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  CK(upload_model(h));
+  if (env_count > h->render_cap) {
+    CK(cudaStreamSynchronize(st));
+    cudaFree(h->render_prims); h->render_prims = nullptr; h->render_cap = 0;
+    CK(cudaMalloc(&h->render_prims, sizeof(float) * 16 * JACO_RENDER_NPRIM * (size_t)env_count));
+    h->render_cap = env_count;
+  }
+  JacoCamera cam;
+  for (int i = 0; i < 3; i++) cam.pos[i] = camera19[i];
+  for (int i = 0; i < 9; i++) cam.R[i] = camera19[3 + i];
+  cam.tan_half_fovy = tanf(0.5f * camera19[12] * 3.14159265358979323846f / 180.0f);
+  cam.znear = camera19[13]; cam.zfar = camera19[14]; cam.ambient = camera19[15];
+  if (!(cam.znear > 0) || !(cam.zfar > cam.znear)) { snprintf(h->err, sizeof h->err, "jaco_render: need 0 < znear < zfar"); return JACO_EINVAL; }
+  for (int k = 0; k < JACO_RENDER_NPRIM; k++) for (int c = 0; c < 3; c++) cam.rgb[k][c] = prim_rgb[3 * k + c];
+  jaco_render_prims_kernel<<<(env_count + 127) / 128, 128, 0, st>>>(h->state, h->n, env_begin, env_count, h->render_prims);
+  dim3 grid((width + JACO_RENDER_TILE - 1) / JACO_RENDER_TILE, (height + JACO_RENDER_TILE - 1) / JACO_RENDER_TILE, env_count);
+  jaco_render_kernel<<<grid, dim3(JACO_RENDER_TILE, JACO_RENDER_TILE), 0, st>>>(cam, h->render_prims, width, height, rgb, depth);
+  h->launches += 2;
+  CK(cudaGetLastError());
+  return JACO_OK;
+}
 int jaco_debug_counters(jaco_handle h, int* out16) {  /* host copy of the work-list counters (synchronises) */
   if (!h || !out16) return JACO_EINVAL;
   CK(cudaMemcpy(out16, h->counters, 16 * sizeof(int), cudaMemcpyDeviceToHost));

@@ -12,11 +12,12 @@
 #define JACO_NOBS 26
 #define JACO_NAUX 72
 #define JACO_NSTATE (JACO_NQ + JACO_NV + JACO_NAUX)  // rows of the SoA state buffer
-#define JACO_MAXCON 32
+#define JACO_MAXCON 32            /* cooperative path: lanes map to contacts */
+#define JACO_MAXCON_GENERAL 48    /* general thread-per-env path (resets with the hand spawned inside / closed around the object: 34-36 contacts) */
 #define JACO_NCH 9
 #define JACO_NBODY 12  // 0 world, 1..9 chain, 10 object, 11 dest
 
-enum { JACO_TASK_REACHING = 0, JACO_TASK_GRASPING = 1, JACO_TASK_PICKING = 2, JACO_TASK_PLACING = 3, JACO_TASK_PICKANDPLACE = 4 };
+enum { JACO_TASK_REACHING = 0, JACO_TASK_GRASPING = 1, JACO_TASK_PICKING = 2, JACO_TASK_PLACING = 3, JACO_TASK_PICKANDPLACE = 4, JACO_TASK_RELEASING = 5, JACO_TASK_CARRYING = 6 };
 enum { JACO_GEOM_PLANE = 0, JACO_GEOM_BOX = 1, JACO_GEOM_CAPSULE = 2 };
 
 // aux[] slots of the per-env state (shared with oracle/jaco_oracle.c jo_get_state)

@@ -196,10 +196,10 @@ JHD void philox4x32(uint64_t seed, uint32_t c0, uint32_t c1, uint32_t c2, uint32
 }
 
 // ------------------------------------------------------------------------------------------- per-env working set
-struct JacoCfg { int task, variant, obs_mode, task_max_steps; uint64_t seed; };
+struct JacoCfg { int task, variant, obs_mode, task_max_steps; uint64_t seed; int binary; };   // binary: the variants' sparse picking reward (cis:56,459,637)
 
 struct JacoSim {
-  static const int MAXC = JACO_MAXCON;
+  static const int MAXC = JACO_MAXCON_GENERAL;
   static JHD const JacoModel& model() { return MDL; }
   // state
   float qpos[JACO_NQ], qvel[JACO_NV], warm[JACO_NV], ctrl[JACO_NU];
@@ -212,11 +212,11 @@ struct JacoSim {
   float Mc[45], Mf[2][21], Lf[2][21];                // chain / free-body inertia (packed), free-body Cholesky factors
   float bias[JACO_NV], fsm[JACO_NV], asm_[JACO_NV], qacc[JACO_NV], fcon[JACO_NV];
   // contacts
-  int ncon, cpair[JACO_MAXCON];
-  float cpos[JACO_MAXCON][3], cn[JACO_MAXCON][3], cdist[JACO_MAXCON];
-  float cD[JACO_MAXCON], cA[JACO_MAXCON][6];         // 1/R of the contact's rows; aref components (A0, B1..B5)
-  float ce[JACO_MAXCON][6], cp[JACO_MAXCON][6];      // (J a - aref) components at the iterate; J p components
-  float cf0[JACO_MAXCON];                            // total normal force (touch sensors)
+  int ncon, cpair[JACO_MAXCON_GENERAL];
+  float cpos[JACO_MAXCON_GENERAL][3], cn[JACO_MAXCON_GENERAL][3], cdist[JACO_MAXCON_GENERAL];
+  float cD[JACO_MAXCON_GENERAL], cA[JACO_MAXCON_GENERAL][6];         // 1/R of the contact's rows; aref components (A0, B1..B5)
+  float ce[JACO_MAXCON_GENERAL][6], cp[JACO_MAXCON_GENERAL][6];      // (J a - aref) components at the iterate; J p components
+  float cf0[JACO_MAXCON_GENERAL];                            // total normal force (touch sensors)
   // joint limits
   int nlim, ldof[5];
   float lsign[5], lD[5], laref[5], le[5], lp[5];
@@ -1460,6 +1460,7 @@ JHD float get_reward(const JacoCfg& cfg, const S& s) {  // util:312-446
     if (s.gripper_pose[2] < 0.1f) r -= 0.1f - s.gripper_pose[2];
     return 0.05f * r;
   }
+  if (cfg.task == JACO_TASK_PICKING && cfg.variant != 0 && cfg.binary) return 0;   // cis:459,500 / trans:465: `if not self.binary ... else: return 0`
   if (cfg.task == JACO_TASK_GRASPING || cfg.task == JACO_TASK_PICKING) {
     float scale = cfg.task == JACO_TASK_GRASPING ? 0.05f : 0.01f;
     float ev[3], down[3] = {0, 0, -1}, up[3] = {0, 0, 1}, xyz[3], tv[3], dv[3];
@@ -1502,15 +1503,23 @@ JHD int terminal_inspection(const JacoCfg& cfg, S& s, float* bonus, float* wb, i
     if (op[2] > oz + 0.07f && (s.touch_index == 1 || s.touch_index == 3)) { *bonus = 200 - s.num_episodes * 0.1f; *succ = 1; return 1; }
     if (op[2] < 0.1f) { *bonus = -20; return 1; }
     return 0;
-  case JACO_TASK_PICKING:
-    if (op[2] > oz + 0.07f && (s.touch_index == 1 || s.touch_index == 3)) { *bonus = 200 - s.num_episodes * 0.1f; *succ = 1; return 1; }
-    if (op[2] < 0.1f) { *bonus = -20; return 1; }
-    return 0;
+  case JACO_TASK_PICKING: {
+    const bool bin = cfg.variant != 0 && cfg.binary;   // cis:637-660 / trans:643-: sparse bonuses 10 / -1 instead of 200 - 0.1 n / -20
+    if (op[2] > oz + 0.07f && (s.touch_index == 1 || s.touch_index == 3)) { *bonus = bin ? 10.0f : 200 - s.num_episodes * 0.1f; *succ = 1; return 1; }
+    if (op[2] < 0.1f) { *bonus = bin ? -1.0f : -20.0f; return 1; }
+    return 0; }
   case JACO_TASK_PLACING: {
     float th = cfg.variant == 0 ? 0.02f : 0.04f;
     if (op[2] < 0.1f) { *bonus = -20; return 1; }
     if (dest_diff < th && s.touch_index == 0 && op[2] < 0.35f) { *bonus = 200 - s.num_episodes * 0.1f; *succ = 1; return 1; }
     if (dest_diff > th && s.touch_index == 0 && op[2] < 0.20f) { *bonus = -20; return 1; }
+    return 0; }
+  case JACO_TASK_CARRYING: return 1;   // util:549-550: (True, 0, wb)
+  case JACO_TASK_RELEASING: {          // util:551-566; obj_velocity = |qvel[9:12]| (mujoco.py:212-215)
+    float ov = sqrtf(s.qvel[9] * s.qvel[9] + s.qvel[10] * s.qvel[10] + s.qvel[11] * s.qvel[11]);
+    if (op[2] < 0.1f) { *bonus = -20; return 1; }
+    if (dest_diff < 0.04f && s.touch_index == 0 && op[2] < 0.35f && ov < 0.01f) { *bonus = 200 - s.num_episodes * 0.1f; *succ = 1; return 1; }
+    if (dest_diff > 0.04f && s.touch_index == 0 && op[2] < 0.20f) { *bonus = -20; return 1; }
     return 0; }
   case JACO_TASK_PICKANDPLACE:
     if (op[2] > oz + 0.07f && (s.touch_index == 1 || s.touch_index == 3) && !s.picked) { s.picked = 1; *bonus = 20; return 0; }
@@ -1572,6 +1581,10 @@ JHD void reset_sample(const JacoCfg& cfg, S& s, int env_id) {
   if (cfg.task == JACO_TASK_REACHING || cfg.task == JACO_TASK_PICKING || cfg.task == JACO_TASK_PICKANDPLACE) {
     ia[0] = uniab(cfg, s, env_id, 0, 0, 0.7f, 2.5f); ia[1] = uniab(cfg, s, env_id, 0, 1, 3.8f, 4.0f); ia[2] = uniab(cfg, s, env_id, 0, 2, 1.0f, 1.7f);
     ia[3] = uniab(cfg, s, env_id, 0, 3, 1.8f, 2.5f); ia[4] = uniab(cfg, s, env_id, 0, 4, 1.0f, 2.5f); ia[5] = uniab(cfg, s, env_id, 0, 5, 0.8f, 2.3f);
+  } else if (cfg.task == JACO_TASK_RELEASING) {   // util:186-189: nine values, the fingers start at 0.6 (mujoco.py:342-346)
+    ia[0] = uniab(cfg, s, env_id, 0, 0, 1.9f, 2.0f); ia[1] = uniab(cfg, s, env_id, 0, 1, 3.3f, 3.6f); ia[2] = uniab(cfg, s, env_id, 0, 2, 0.5f, 0.8f);
+    ia[3] = uniab(cfg, s, env_id, 0, 3, 1.8f, 2.5f); ia[4] = uniab(cfg, s, env_id, 0, 4, 1.3f, 2.0f); ia[5] = uniab(cfg, s, env_id, 0, 5, -0.4f, -0.9f);
+    s.qpos[6] = s.qpos[7] = s.qpos[8] = 0.6f;
   } else {
     float c0 = uniab(cfg, s, env_id, 0, 0, 3 * JPI / 8, JPI / 2), c1 = uniab(cfg, s, env_id, 0, 1, JPI / 2, 5 * JPI / 8);
     ia[0] = uni(cfg, s, env_id, 0, 6) < 0.5f ? c0 : c1; ia[1] = 3.85f; ia[2] = uniab(cfg, s, env_id, 0, 2, 1.0f, 1.1f);
@@ -1600,7 +1613,8 @@ JHD void env_reset(const JacoCfg& cfg, JacoSim& s, int env_id, float* obs) {
   const JacoModel& m = MDL;
   reset_sample(cfg, s, env_id);
   for (int i = 0; i < JACO_NU; i++) s.ctrl[i] = 0;
-  if (cfg.task == JACO_TASK_PLACING) {  // util:106-117: hold the object in the hand for 150 settle substeps
+  const bool held = cfg.task == JACO_TASK_PLACING || cfg.task == JACO_TASK_RELEASING || cfg.task == JACO_TASK_CARRYING;   // util:106
+  if (held) {  // util:106-117: hold the object in the hand for 150 settle substeps
     mj_forward(s, false);
     float p[3], t[3], eul[3], q[4], dp[3], off[3] = {-0.04f, 0, 0}, u[6];
     m3mulv(t, s.bR[6], m.ee_obj_off); v3add(p, s.bx[6], t);
@@ -1624,7 +1638,7 @@ JHD void env_reset(const JacoCfg& cfg, JacoSim& s, int env_id, float* obs) {
     mj_forward(s, true);
   }
   if (cfg.task == JACO_TASK_REACHING) { for (int i = 0; i < 6; i++) s.target[i] = s.reach_goal[i]; }
-  else if (cfg.task == JACO_TASK_GRASPING) {
+  else if (cfg.task == JACO_TASK_GRASPING || cfg.task == JACO_TASK_CARRYING) {
     // util:123-167: two approach servo loops.  Unbounded `while True` in the reference; bounded here (JACO_GRASP_RESET_MAX substeps
     // each: 4 s of simulated time, the approach takes ~0.5-1.5 s at the controller's 0.4 m/s limit).
     get_gripper_pose(s);
@@ -1655,7 +1669,7 @@ JHD void env_reset(const JacoCfg& cfg, JacoSim& s, int env_id, float* obs) {
       if (v3norm(d) < 0.15f) break;
     }
   }
-  else if (cfg.task != JACO_TASK_PLACING) { get_gripper_pose(s); for (int i = 0; i < 6; i++) s.target[i] = s.gripper_pose[i]; }
+  else if (!held) { get_gripper_pose(s); for (int i = 0; i < 6; i++) s.target[i] = s.gripper_pose[i]; }
   get_observation(cfg, s, env_id, obs);
   s.rng_counter += 1;
 }
@@ -1678,7 +1692,7 @@ JHD void env_step(const JacoCfg& cfg, JacoSim& s, int env_id, const float* actio
   if (s.current_steps < cfg.task_max_steps) d = terminal_inspection(cfg, s, &bonus, &w, &sc);
   else { d = 1; bonus = -10; w = 0; sc = 0; }
   // cause: 0 running, 1 success, 2 time-out, 3 singular exit, 4 drop / -20 exit, 5 other
-  if (cause) *cause = !d ? 0 : (sc ? 1 : (s.current_steps >= cfg.task_max_steps ? 2 : (bonus == -1.0f ? 3 : (bonus == -20.0f ? 4 : 5))));
+  if (cause) *cause = !d ? 0 : (sc ? 1 : (s.current_steps >= cfg.task_max_steps ? 2 : (JPI - 0.1f < s.qpos[2] && s.qpos[2] < JPI + 0.1f ? 3 : (bonus < 0 ? 4 : 5))));
   *reward = r + bonus; *done = d; *succ = sc; *wb = w;
   s.rng_counter += 1;
 }

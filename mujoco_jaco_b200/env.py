@@ -18,10 +18,40 @@ from . import _lib
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 NQ, NV, NU, NOBS, NACT, NAUX, NSTATS = 23, 21, 9, 26, 7, 72, 16
-TASKS = {"reaching": 0, "grasping": 1, "picking": 2, "placing": 3, "pickAndplace": 4}
+TASKS = {"reaching": 0, "grasping": 1, "picking": 2, "placing": 3, "pickAndplace": 4, "releasing": 5, "carrying": 6}
 VARIANTS = {"base": 0, "cis": 1, "trans": 2}
 STAT_NAMES = ["episodes", "successes", "return_sum", "timeouts", "drops", "singular_exits", "nan_resets",
               "env_steps", "length_sum"]
+
+
+# Camera 0 of the reference's model: <camera fovy="60"/> default class (jaco2_curtain_torque.xml:9) and
+# <camera name="visual_camera" pos="0 0.2 0.5" euler="1.3 0 0"> (xml:286; compiler angle="radian", default eulerseq "xyz").
+CAMERA0 = dict(pos=(0.0, 0.2, 0.5), euler=(1.3, 0.0, 0.0), fovy=60.0)
+RENDER_PRIMS = 35      # include/jaco_b200.h JACO_RENDER_PRIMS: the 33 compiled geoms + 2 upper-arm "bone" capsules
+
+
+def camera_vector(pos=CAMERA0["pos"], euler=CAMERA0["euler"], fovy=CAMERA0["fovy"], extent=1.0, znear=0.01, zfar=50.0, ambient=0.35):
+    """float32[19] for jaco_render: pos, R = Rx Ry Rz (MuJoCo's intrinsic xyz euler sequence; columns = camera right / up / backward),
+    fovy (degrees), znear * extent, zfar * extent (MuJoCo: vis.map.znear / zfar scaled by stat.extent), ambient."""
+    a, b, c = euler
+    Rx = np.array([[1, 0, 0], [0, np.cos(a), -np.sin(a)], [0, np.sin(a), np.cos(a)]])
+    Ry = np.array([[np.cos(b), 0, np.sin(b)], [0, 1, 0], [-np.sin(b), 0, np.cos(b)]])
+    Rz = np.array([[np.cos(c), -np.sin(c), 0], [np.sin(c), np.cos(c), 0], [0, 0, 1]])
+    return np.concatenate([np.asarray(pos, np.float64), (Rx @ Ry @ Rz).reshape(-1), [fovy, znear * extent, zfar * extent, ambient, 0, 0, 0]]).astype(np.float32)
+
+
+def render_palette(geom_names=None):
+    """Flat colours per primitive (float32[35, 3]): the reference's materials live in its meshes / GL path, unavailable here."""
+    rgb = np.tile(np.array([0.75, 0.75, 0.75], np.float32), (RENDER_PRIMS, 1))
+    rgb[0] = (0.55, 0.55, 0.55)        # floor
+    rgb[1] = (0.50, 0.35, 0.20)        # object holder
+    rgb[2] = (0.00, 0.00, 0.50)        # object (xml: rgba="0 0 0.5 0.8")
+    rgb[3] = (0.20, 0.50, 0.20)        # destination box
+    rgb[4:23] = (0.90, 0.80, 0.10)     # touch pads
+    rgb[23:29] = (0.70, 0.70, 0.72)    # finger capsules
+    rgb[29] = (0.30, 0.30, 0.32)       # hand
+    rgb[30:35] = (0.22, 0.22, 0.25)    # fore-arm links and upper-arm bones
+    return rgb
 
 
 def load_model_blob(robot_file="jaco2_curtain_torque"):
@@ -40,7 +70,7 @@ class JacoVecEnv:
     """Batched Jaco environment on one GPU (one independent shard of the global env range)."""
 
     def __init__(self, n_envs, task="picking", variant="base", obs_mode=1, seed=0, device=0, env_offset=0,
-                 robot_file="jaco2_curtain_torque", auto_reset=True, model_blob=None):
+                 robot_file="jaco2_curtain_torque", auto_reset=True, model_blob=None, binary=False):
         if not torch.cuda.is_available():
             raise RuntimeError("JacoVecEnv needs a CUDA device: mujoco_jaco_b200 has no CPU fallback")
         if task not in TASKS:
@@ -52,7 +82,7 @@ class JacoVecEnv:
         blob = load_model_blob(robot_file) if model_blob is None else np.ascontiguousarray(model_blob, np.float64)
         h = C.c_void_p()
         rc = self.L.jaco_create(blob.ctypes.data_as(C.c_void_p), blob.nbytes, self.n_envs, TASKS[task],
-                                VARIANTS[variant] | (obs_mode << 4), device, seed, env_offset, C.byref(h))
+                                VARIANTS[variant] | (obs_mode << 4) | (int(bool(binary)) << 8), device, seed, env_offset, C.byref(h))
         if rc != 0:
             msg = self.L.jaco_last_error(h).decode() if h else ""
             raise RuntimeError(f"jaco_create failed ({rc}) {msg}")
@@ -120,6 +150,19 @@ class JacoVecEnv:
             a = torch.nn.functional.pad(a, (0, NAUX - a.shape[1]))
         self._check(self.L.jaco_set_state(self.h, _ptr(q), _ptr(v), _ptr(a), self._stream()))
         torch.cuda.current_stream(self.device).synchronize()  # keep q/v/a alive until consumed
+
+    def render(self, env_begin=0, env_count=None, width=640, height=480, camera=None, palette=None):
+        """_get_camera (util:302-307) for a range of envs: (rgb uint8 [k, H, W, 3] with row 0 at the top, depth float32 [k, H, W],
+        OpenGL-normalised like MjRenderContextOffscreen.read_pixels(depth=True)).  Headless CUDA ray caster; see csrc/jaco_render.cuh."""
+        k = self.n_envs - env_begin if env_count is None else int(env_count)
+        cam = np.ascontiguousarray(camera_vector() if camera is None else camera, np.float32)
+        pal = np.ascontiguousarray(render_palette() if palette is None else palette, np.float32)
+        assert cam.shape == (19,) and pal.shape == (RENDER_PRIMS, 3)
+        rgb = torch.empty(k, height, width, 3, dtype=torch.uint8, device=self.device)
+        depth = torch.empty(k, height, width, dtype=torch.float32, device=self.device)
+        self._check(self.L.jaco_render(self.h, cam.ctypes.data_as(C.c_void_p), pal.ctypes.data_as(C.c_void_p), int(width), int(height),
+                                       int(env_begin), k, _ptr(rgb), _ptr(depth), self._stream()))
+        return rgb, depth
 
     def debug_substep(self, ctrl):
         n, dev = self.n_envs, self.device
@@ -253,6 +296,12 @@ class JacoMujocoEnv:
     def close(self):
         self._vec.close()
         return None
+
+    def _get_camera(self):
+        """util:302-307: (image uint8 [480, 640, 3], depth float32 [480, 640]), both top-down.  Headless CUDA ray caster over the
+        simulation's primitives instead of the reference's OpenGL off-screen context (unavailable on this box)."""
+        rgb, depth = self._vec.render(0, 1, 640, 480)
+        return rgb[0].cpu().numpy(), depth[0].cpu().numpy()
 
     def set_capture_path(self, path):
         raise NotImplementedError("viewer / GL capture: unavailable on this box")

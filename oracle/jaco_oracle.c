@@ -185,7 +185,7 @@ struct jo_env {
   real w_jar[JO_MAXEFC], w_jp[JO_MAXEFC], w_bp[JO_MAXEFC];
   real efc_J[JO_MAXEFC][NV], efc_pos[JO_MAXEFC], efc_D[JO_MAXEFC], efc_aref[JO_MAXEFC], efc_force[JO_MAXEFC];
   /* env logic (env_mujoco_util.py) */
-  int task, variant, obs_mode, env_id; uint64_t seed; uint32_t rng_counter;
+  int task, variant, obs_mode, binary, env_id; uint64_t seed; uint32_t rng_counter;
   real target[6], gripper_angle, ramp[50];
   int gripper_iter, action_in, picked, touch_index, num_episodes, current_steps, task_max_steps;
   real obj_goal[3], dest_goal[3], reach_goal[6];
@@ -1015,6 +1015,7 @@ static real get_reward(jo_env *e) { /* util:312-446 */
     if (e->gripper_pose[2] < R_(0.1)) r -= R_(0.1) - e->gripper_pose[2];
     return R_(0.05) * r;
   }
+  if (e->task == JO_TASK_PICKING && e->variant != JO_VAR_BASE && e->binary) return 0; /* cis:459,500 / trans:465 */
   if (e->task == JO_TASK_GRASPING || e->task == JO_TASK_PICKING) {
     real scale = e->task == JO_TASK_GRASPING ? R_(0.05) : R_(0.01);
     real ev[3], down[3] = {0, 0, -1}, up[3] = {0, 0, 1}, xyz[3], tv[3], dv[3];
@@ -1058,15 +1059,23 @@ static int terminal_inspection(jo_env *e, real *bonus, real *wb, int *succ) {
     if (op[2] > oz + R_(0.07) && (e->touch_index == 1 || e->touch_index == 3)) { *bonus = 200 - e->num_episodes * R_(0.1); *succ = 1; return 1; }
     if (op[2] < R_(0.1)) { *bonus = -20; return 1; }
     return 0; }
-  case JO_TASK_PICKING:
-    if (op[2] > oz + R_(0.07) && (e->touch_index == 1 || e->touch_index == 3)) { *bonus = 200 - e->num_episodes * R_(0.1); *succ = 1; return 1; }
-    if (op[2] < R_(0.1)) { *bonus = -20; return 1; }
-    return 0;
+  case JO_TASK_PICKING: {
+    const int bin = e->variant != JO_VAR_BASE && e->binary; /* cis:637-660 / trans:643-: sparse bonuses 10 / -1 */
+    if (op[2] > oz + R_(0.07) && (e->touch_index == 1 || e->touch_index == 3)) { *bonus = bin ? R_(10) : 200 - e->num_episodes * R_(0.1); *succ = 1; return 1; }
+    if (op[2] < R_(0.1)) { *bonus = bin ? R_(-1) : R_(-20); return 1; }
+    return 0; }
   case JO_TASK_PLACING: {
     real th = e->variant == JO_VAR_BASE ? R_(0.02) : R_(0.04);
     if (op[2] < R_(0.1)) { *bonus = -20; return 1; }
     if (dest_diff < th && e->touch_index == 0 && op[2] < R_(0.35)) { *bonus = 200 - e->num_episodes * R_(0.1); *succ = 1; return 1; }
     if (dest_diff > th && e->touch_index == 0 && op[2] < R_(0.20)) { *bonus = -20; return 1; }
+    return 0; }
+  case JO_TASK_CARRYING: return 1; /* util:549-550: (True, 0, wb) */
+  case JO_TASK_RELEASING: { /* util:551-566; obj_velocity = |qvel[9:12]| (mujoco.py:212-215) */
+    real ov = rsqrt_(e->qvel[9] * e->qvel[9] + e->qvel[10] * e->qvel[10] + e->qvel[11] * e->qvel[11]);
+    if (op[2] < R_(0.1)) { *bonus = -20; return 1; }
+    if (dest_diff < R_(0.04) && e->touch_index == 0 && op[2] < R_(0.35) && ov < R_(0.01)) { *bonus = 200 - e->num_episodes * R_(0.1); *succ = 1; return 1; }
+    if (dest_diff > R_(0.04) && e->touch_index == 0 && op[2] < R_(0.20)) { *bonus = -20; return 1; }
     return 0; }
   case JO_TASK_PICKANDPLACE:
     if (op[2] > oz + R_(0.07) && (e->touch_index == 1 || e->touch_index == 3) && !e->picked) { e->picked = 1; *bonus = 20; return 0; }
@@ -1120,6 +1129,10 @@ void jo_reset(jo_env *e, float *obs) { /* env_mujoco.py:99-102 -> util:92-174 */
   if (e->task == JO_TASK_REACHING || e->task == JO_TASK_PICKING || e->task == JO_TASK_PICKANDPLACE) {
     ia[0] = uniab(e, 0, 0, 0.7, 2.5); ia[1] = uniab(e, 0, 1, 3.8, 4); ia[2] = uniab(e, 0, 2, 1, 1.7);
     ia[3] = uniab(e, 0, 3, 1.8, 2.5); ia[4] = uniab(e, 0, 4, 1, 2.5); ia[5] = uniab(e, 0, 5, 0.8, 2.3);
+  } else if (e->task == JO_TASK_RELEASING) { /* util:186-189: nine values, the fingers start at 0.6 (mujoco.py:342-346) */
+    ia[0] = uniab(e, 0, 0, 1.9, 2); ia[1] = uniab(e, 0, 1, 3.3, 3.6); ia[2] = uniab(e, 0, 2, 0.5, 0.8);
+    ia[3] = uniab(e, 0, 3, 1.8, 2.5); ia[4] = uniab(e, 0, 4, 1.3, 2); ia[5] = uniab(e, 0, 5, -0.4, -0.9);
+    e->qpos[6] = e->qpos[7] = e->qpos[8] = R_(0.6);
   } else {
     real c0 = uniab(e, 0, 0, 3 * 3.14159265358979323846 / 8, 3.14159265358979323846 / 2), c1 = uniab(e, 0, 1, 3.14159265358979323846 / 2, 5 * 3.14159265358979323846 / 8);
     ia[0] = uni(e, 0, 6) < R_(0.5) ? c0 : c1; ia[1] = R_(3.85); ia[2] = uniab(e, 0, 2, 1, 1.1);
@@ -1151,7 +1164,8 @@ void jo_reset(jo_env *e, float *obs) { /* env_mujoco.py:99-102 -> util:92-174 */
     for (int i = 16; i < NV; i++) e->qvel[i] = 0;
   }
   mj_forward(e);
-  if (e->task == JO_TASK_PLACING) { /* util:106-117: object held in the hand for 150 settle substeps */
+  const int held = e->task == JO_TASK_PLACING || e->task == JO_TASK_RELEASING || e->task == JO_TASK_CARRYING; /* util:106 */
+  if (held) { /* util:106-117: object held in the hand for 150 settle substeps */
     real R6[9], p[3], t[3], eul[3], q[4], dp[3], off[3] = {R_(-0.04), 0, 0};
     memcpy(R6, e->xmat[6], sizeof R6);
     m3mulv(t, R6, e->ee_obj_off); v3add(p, e->xpos[6], t);
@@ -1167,7 +1181,7 @@ void jo_reset(jo_env *e, float *obs) { /* env_mujoco.py:99-102 -> util:92-174 */
     set_obj(e, e->obj_goal, zq);
   }
   if (e->task == JO_TASK_REACHING) memcpy(e->target, e->reach_goal, sizeof e->target);
-  else if (e->task == JO_TASK_GRASPING) { /* util:123-167: two approach servo loops (unbounded in the reference; bounded here, JO_GRASP_RESET_MAX substeps each) */
+  else if (e->task == JO_TASK_GRASPING || e->task == JO_TASK_CARRYING) { /* util:123-167: two approach servo loops (unbounded in the reference; bounded here, JO_GRASP_RESET_MAX substeps each) */
     get_gripper_pose(e);
     real d[3]; v3sub(d, e->obj_goal, e->gripper_pose);
     real sx = d[0] > 0 ? R_(1) : (d[0] < 0 ? R_(-1) : R_(0));
@@ -1196,7 +1210,7 @@ void jo_reset(jo_env *e, float *obs) { /* env_mujoco.py:99-102 -> util:92-174 */
       if (v3norm(d) < R_(0.15)) break;
     }
   }
-  else if (e->task != JO_TASK_PLACING) { get_gripper_pose(e); memcpy(e->target, e->gripper_pose, sizeof e->target); } /* util:65 (ctor) */
+  else if (!held) { get_gripper_pose(e); memcpy(e->target, e->gripper_pose, sizeof e->target); } /* util:65 (ctor) */
   get_observation(e, obs);
   e->rng_counter += 1;
 }
@@ -1224,8 +1238,8 @@ jo_env *jo_create(const double *blob, int nblob, int task, int variant, uint64_t
   if (nblob != JM_TOTAL) return 0;
   jo_env *e = (jo_env *)calloc(1, sizeof(jo_env));
   load_model(e, blob);
-  e->task = task; e->variant = variant & 15; e->obs_mode = (variant >> 4) & 15; e->seed = seed; e->env_id = env_id;
-  e->task_max_steps = (task == JO_TASK_REACHING || task == JO_TASK_GRASPING) ? 500 : ((task == JO_TASK_PICKING || task == JO_TASK_PLACING) ? 700 : 1200);
+  e->task = task; e->variant = variant & 15; e->obs_mode = (variant >> 4) & 15; e->binary = (variant >> 8) & 1; e->seed = seed; e->env_id = env_id;
+  e->task_max_steps = (task == JO_TASK_REACHING || task == JO_TASK_GRASPING || task == JO_TASK_RELEASING || task == JO_TASK_CARRYING) ? 500 : ((task == JO_TASK_PICKING || task == JO_TASK_PLACING) ? 700 : 1200);
   float obs[JO_OBS];
   jo_reset(e, obs);
   e->rng_counter = 0;
@@ -1290,6 +1304,33 @@ void jo_forward(jo_env *e, const double *ctrl, double *M, double *bias, double *
   if (qacc) for (int i = 0; i < NV; i++) qacc[i] = e->qacc[i];
   if (ncon) *ncon = e->ncon;
   if (sensordata) for (int i = 0; i < 20; i++) sensordata[i] = e->sensordata[i];
+}
+/* world primitives the headless camera draws (restates mujoco_jaco_b200/csrc/jaco_render.cuh render_prims; util:302-307 is an OpenGL
+ * call in the reference): per primitive pos[3], R[9] row-major, size[3], type; the model's geoms, then two capsules (radius 0.04)
+ * between the origins of bodies 1-2 and 2-3 for the upper-arm links that carry no collision geom.  Evaluated at the current qpos. */
+int jo_render_prims(jo_env *e, double *out, int maxprim) {
+  kinematics(e);
+  int n = 0;
+  for (int g = 0; g < JM_NGEOM && n < maxprim; g++, n++) {
+    real p[3], R[9]; geom_world(e, g, p, R);
+    double *o = out + 16 * n;
+    for (int i = 0; i < 3; i++) { o[i] = p[i]; o[12 + i] = e->geoms[g].size[i]; }
+    for (int i = 0; i < 9; i++) o[3 + i] = R[i];
+    o[15] = e->geoms[g].type;
+  }
+  for (int b = 0; b < 2 && n < maxprim; b++, n++) {
+    double *o = out + 16 * n, d[3], len = 0;
+    for (int i = 0; i < 3; i++) { d[i] = (double)e->xpos[b + 2][i] - (double)e->xpos[b + 1][i]; len += d[i] * d[i]; o[i] = 0.5 * ((double)e->xpos[b + 1][i] + (double)e->xpos[b + 2][i]); }
+    len = sqrt(len);
+    if (len < 1e-6) { d[0] = 0; d[1] = 0; d[2] = 1; len = 0; } else for (int i = 0; i < 3; i++) d[i] /= len;
+    double a[3] = {1, 0, 0}; if (fabs(d[0]) > 0.9) { a[0] = 0; a[1] = 1; }
+    double x[3] = {a[1] * d[2] - a[2] * d[1], a[2] * d[0] - a[0] * d[2], a[0] * d[1] - a[1] * d[0]}, nx = sqrt(x[0] * x[0] + x[1] * x[1] + x[2] * x[2]);
+    for (int i = 0; i < 3; i++) x[i] /= nx;
+    double y[3] = {d[1] * x[2] - d[2] * x[1], d[2] * x[0] - d[0] * x[2], d[0] * x[1] - d[1] * x[0]};
+    for (int i = 0; i < 3; i++) { o[3 + 3 * i] = x[i]; o[4 + 3 * i] = y[i]; o[5 + 3 * i] = d[i]; }
+    o[12] = 0.04; o[13] = 0.5 * len; o[14] = 0; o[15] = 2;
+  }
+  return n;
 }
 int jo_get_contacts(const jo_env *e, double *out, int maxcon) {
   int n = e->ncon < maxcon ? e->ncon : maxcon;

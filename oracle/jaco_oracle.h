@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-enum { JO_TASK_REACHING = 0, JO_TASK_GRASPING = 1, JO_TASK_PICKING = 2, JO_TASK_PLACING = 3, JO_TASK_PICKANDPLACE = 4 };
+enum { JO_TASK_REACHING = 0, JO_TASK_GRASPING = 1, JO_TASK_PICKING = 2, JO_TASK_PLACING = 3, JO_TASK_PICKANDPLACE = 4, JO_TASK_RELEASING = 5, JO_TASK_CARRYING = 6 };
 enum { JO_VAR_BASE = 0, JO_VAR_CIS = 1, JO_VAR_TRANS = 2 };
 
 #define JO_NQ 23

@@ -13,7 +13,7 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 REPO = os.path.dirname(HERE)
-TASKS = {"reaching": 0, "grasping": 1, "picking": 2, "placing": 3, "pickAndplace": 4}
+TASKS = {"reaching": 0, "grasping": 1, "picking": 2, "placing": 3, "pickAndplace": 4, "releasing": 5, "carrying": 6}
 VARIANTS = {"base": 0, "cis": 1, "trans": 2}
 NQ, NV, NU, NOBS, NAUX = 23, 21, 9, 26, 64
 _dp = C.POINTER(C.c_double)
@@ -60,6 +60,8 @@ def lib(f32=False, fast=False):
         L.jo_forward.argtypes = [C.c_void_p, _dp, _dp, _dp, _dp, _dp, _dp, _dp, _ip, _dp]
         L.jo_get_contacts.argtypes = [C.c_void_p, _dp, C.c_int]
         L.jo_get_contacts.restype = C.c_int
+        L.jo_render_prims.argtypes = [C.c_void_p, _dp, C.c_int]
+        L.jo_render_prims.restype = C.c_int
         L.jo_osc.argtypes = [C.c_void_p] + [_dp] * 8
         L.jo_solver_stats.argtypes = [C.c_void_p, _ip, _dp, _ip]
         L.jo_touch_knife_edge.argtypes = [C.c_void_p]
@@ -78,10 +80,10 @@ def _d(a):
 class OracleEnv:
     """One reference-semantics environment on the CPU (JacoMujocoEnv restated)."""
 
-    def __init__(self, task="picking", variant="base", obs_mode=1, seed=0, env_id=0, f32=False, blob=None, fast=False):
+    def __init__(self, task="picking", variant="base", obs_mode=1, seed=0, env_id=0, f32=False, blob=None, fast=False, binary=False):
         self.L = lib(f32, fast)
         self.blob = load_blob() if blob is None else blob
-        v = VARIANTS[variant] | (obs_mode << 4)
+        v = VARIANTS[variant] | (obs_mode << 4) | (int(bool(binary)) << 8)
         self.h = self.L.jo_create(_d(self.blob), len(self.blob), TASKS[task], v, seed, env_id)
         if not self.h:
             raise RuntimeError("jo_create failed (blob size mismatch?)")
@@ -135,6 +137,12 @@ class OracleEnv:
     def contacts(self, maxcon=96):
         out = np.zeros((maxcon, 10))
         n = self.L.jo_get_contacts(self.h, _d(out), maxcon)
+        return out[:n]
+
+    def render_prims(self, maxprim=64):
+        """world primitives of the headless camera at the current qpos: float64 [n, 16] = pos 3, R 9 (row-major), size 3, type"""
+        out = np.zeros((maxprim, 16))
+        n = self.L.jo_render_prims(self.h, _d(out), maxprim)
         return out[:n]
 
     def osc(self, J, M, bias, ee_pos, ee_quat, dq, target):

@@ -9,8 +9,8 @@
 extern "C" {
 void hh_init(const double* blob) { jaco_model_from_blob(blob, &g_jaco_model_host); }
 static JacoCfg mkcfg(int task, int variant, unsigned long long seed) {
-  JacoCfg c; c.task = task; c.variant = variant & 15; c.obs_mode = (variant >> 4) & 15; c.seed = seed;
-  c.task_max_steps = (task == 0 || task == 1) ? 500 : ((task == 2 || task == 3) ? 700 : 1200);
+  JacoCfg c; c.task = task; c.variant = variant & 15; c.obs_mode = (variant >> 4) & 15; c.binary = (variant >> 8) & 1; c.seed = seed;
+  c.task_max_steps = (task == 0 || task == 1 || task == 5 || task == 6) ? 500 : ((task == 2 || task == 3) ? 700 : 1200);
   return c;
 }
 void hh_reset(int task, int variant, unsigned long long seed, int env_offset, float* state, int N, float* obs) {

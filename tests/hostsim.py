@@ -15,7 +15,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 REPO = os.path.dirname(HERE)
 NQ, NV, NU, NOBS, NAUX = 23, 21, 9, 26, 72
 NSTATE = NQ + NV + NAUX
-TASKS = {"reaching": 0, "grasping": 1, "picking": 2, "placing": 3, "pickAndplace": 4}
+TASKS = {"reaching": 0, "grasping": 1, "picking": 2, "placing": 3, "pickAndplace": 4, "releasing": 5, "carrying": 6}
 VARIANTS = {"base": 0, "cis": 1, "trans": 2}
 _f = C.POINTER(C.c_float)
 _lib = None
@@ -53,10 +53,10 @@ def fp(a):
 
 
 class HostSim:
-    def __init__(self, n, task="picking", variant="base", obs_mode=1, seed=0, env_offset=0):
+    def __init__(self, n, task="picking", variant="base", obs_mode=1, seed=0, env_offset=0, binary=False):
         self.L = lib()
         self.n, self.task, self.seed, self.env_offset = n, TASKS[task], seed, env_offset
-        self.variant = VARIANTS[variant] | (obs_mode << 4)
+        self.variant = VARIANTS[variant] | (obs_mode << 4) | (int(bool(binary)) << 8)
         self.state = np.zeros((NSTATE, n), np.float32)
         self.stats = np.zeros(16, np.float32)
 
@@ -129,7 +129,7 @@ class HostSim:
         Mc, bias, J = np.zeros(45, np.float32), np.zeros(21, np.float32), np.zeros((6, 6), np.float32)
         p, q, a = np.zeros(3, np.float32), np.zeros(4, np.float32), np.zeros(21, np.float32)
         ncon, it = C.c_int(), C.c_int()
-        con = np.zeros((32, 8), np.float32)
+        con = np.zeros((48, 8), np.float32)
         self.L.hh_forward(fp(self.state), self.n, i, fp(c), fp(Mc), fp(bias), fp(J), fp(p), fp(q), fp(a),
                           C.byref(ncon), C.byref(it), fp(con))
         M = np.zeros((9, 9), np.float32)

@@ -181,3 +181,33 @@ def test_config4_tasks_and_variants_one_step(task, variant):
     o64, _, (kd, kc) = live_answers_and_knife_edges(task, q, v, aux[:, :64], act=a, variant=variant, seed=13)
     o1, r1, d1, s1 = [t_.cpu().numpy() for t_ in env.step(torch.from_numpy(a).cuda())]
     check_step(f"{task}/{variant}", dict(obs=o1, reward=r1, done=d1, succ=s1), o64, kd, kc, max_discrete_frac=0.35 if task == "placing" else 0.1)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("task", ["releasing", "carrying"])
+def test_releasing_and_carrying_reset_and_step(task):
+    """the releasing / carrying branches (util:106-117 in-hand start, util:186-189 nine init angles, util:123-167 servo loops
+    for carrying, util:549-566 terminal logic, reward 0, task_max_steps 500): reset against the oracle where the oracle's own float32
+    build reproduces its float64 reset, then one env step from the kernel's injected state (done / succ exact, reward 1e-5)."""
+    from mujoco_jaco_b200.env import JacoVecEnv
+    n = 64
+    env = JacoVecEnv(n, task=task, seed=29, auto_reset=False)
+    obs = env.reset().cpu().numpy()
+    ora = _oracles(task, 29, n)
+    oobs = np.stack([o.reset() for o in ora])
+    o32 = np.stack([o.reset() for o in _oracles(task, 29, n, f32=True)])
+    tol = 2e-3
+    ke = np.abs(o32 - oobs).max(1) > tol / 4
+    print(f"{task} reset: {int(ke.sum())} of {n} envs excluded (oracle float32 vs float64 reset differ)")
+    assert ke.mean() < 0.3
+    assert (np.abs(obs - oobs).max(1) <= tol)[~ke].all(), np.abs(obs - oobs).max(1)
+    q, v, aux = [t_.cpu().numpy() for t_ in env.get_state()]
+    if task == "releasing":
+        assert np.abs(q[:, 5] + 0.65).max() <= 0.26 and (np.abs(obs[:, 8:11] - obs[:, 1:4]).max(1) < 0.12).all()   # object in the hand
+    a = np.random.default_rng(31).uniform(-1, 1, (n, 7)).astype(np.float32)
+    o64, _, (kd, kc) = live_answers_and_knife_edges(task, q, v, aux[:, :64], act=a, seed=29)
+    o1, r1, d1, s1 = [t_.cpu().numpy() for t_ in env.step(torch.from_numpy(a).cuda())]
+    check_step(task, dict(obs=o1, reward=r1, done=d1, succ=s1), o64, kd, kc, max_discrete_frac=0.35)
+    if task == "carrying":
+        assert d1.all() and not s1.any()       # util:549-550: (True, 0, wb) on every step
+    env.close()
