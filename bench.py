@@ -148,6 +148,11 @@ def main():
     ap.add_argument("--age-steps", type=int, default=200,
                     help="untimed roll-out steps before the warm-up (SURVEY 8d C3: 200): the workload drifts as episodes age "
                          "(more arm-scene contacts), so timing straight after reset() would measure an easier mix")
+    ap.add_argument("--action-bank", type=int, default=0,
+                    help="0 (default): a fresh U(-1,1)^7 action batch is drawn on the device for every step, outside the timed region "
+                         "(BASELINE config 3 'actions U(-1,1)^7', what the CPU arm does too); K > 0: cycle through K pre-generated batches "
+                         "(rounds 1-2 used K = 32: every env then repeats a 32-step action sequence whose net displacement walks the arm "
+                         "into the singular posture, a harder mix than i.i.d. actions)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-contact-rich", action="store_true", help="skip the secondary contact-rich line (SURVEY 8d C3-ii)")
@@ -188,7 +193,8 @@ def main():
     env = JacoVecEnv(n, task=args.task, seed=0, device=local, env_offset=env_offset, auto_reset=True)
     env.reset()
     gen = torch.Generator(device=dev); gen.manual_seed(1234 + rank)
-    actions = torch.rand(32, n, NACT, device=dev, generator=gen) * 2 - 1   # resident in HBM before timing
+    bank = max(args.action_bank, 0)
+    actions = torch.rand(max(bank, 8), n, NACT, device=dev, generator=gen) * 2 - 1   # action bank (and the contact-rich line's actions)
 
     def barrier():
         torch.cuda.synchronize()
@@ -200,7 +206,9 @@ def main():
         """the step's action batch on the device: config 3 = pre-generated U(-1,1)^7, config 5 = composite policy forward on the
         env's own observation buffer (no host round trip)"""
         if policy is None:
-            return actions[i % 32]
+            if bank:
+                return actions[i % bank]
+            return torch.rand(n, NACT, device=dev, generator=gen) * 2 - 1     # fresh i.i.d. batch, resident in HBM before the timed region
         with torch.no_grad():
             return policy(env.obs, deterministic=False)[0]
 
@@ -232,11 +240,14 @@ def main():
     barrier()
     for i in range(K):
         flush.fill_(i & 255)
+        a_dev = act(W + i) if policy is None else None    # config 3: the action batch exists in HBM before the timed region starts
         ev0[i].record()
-        env.step(act(W + i))                           # config 5: the policy forward is inside the timed region
+        env.step(a_dev if policy is None else act(W + i))   # config 5: the policy forward is inside the timed region
         ev1[i].record()
         flush.fill_((i + 1) & 255)
         torch.cuda.synchronize()
+        if policy is None and not bank:
+            a_hosts[i % len(a_hosts)].uniform_(-1, 1)        # fresh host actions for this e2e step (pinned, in place), outside the timed region
         t0 = time.perf_counter()
         if policy is None:
             env.step_host(a_nps[i % len(a_nps)], outs_np)   # returns after its own stream synchronisation
@@ -309,6 +320,9 @@ def main():
                                     "grasping 11-128^3-14, meta 17-256^3-3; random-initialised weights of the saved architecture, stochastic actions) "
                                     "forward in PyTorch fp32 + env step on the device, no host round trip"),
                        "baseline_config": args.config,
+                       "actions": ("policy" if policy is not None else ("fresh i.i.d. U(-1,1)^7 batch per step, drawn on the device outside the timed region "
+                                   "(like the CPU arm's per-step rng.uniform)" if not bank else
+                                   f"bank of {bank} pre-generated batches, cycled (the rounds 1-2 protocol: periodic actions walk the arms into the singular posture)")),
                        "envs_per_gpu": n, "substeps_per_step": 50,
                        "episode_age": f"{args.age_steps} untimed roll-out steps after reset() before the {W} warm-up steps "
                                       "(step time grows with episode age, profiles/r01_step_time_trend.log)",

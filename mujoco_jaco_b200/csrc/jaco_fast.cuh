@@ -1304,7 +1304,7 @@ JHD JNOINLINE int fast_reset(const JacoCfg& cfg, FastSim& s, int env_id, float* 
 // warp must then call this function together (lanes without an environment pass active = false).
 template <bool COOP>
 JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* action, float* obs, float* reward, int* done, int* succ, float* wb, int* why,
-                      CoopWS* ws = nullptr, bool active = true, int* cause = nullptr, float* lst = nullptr) {
+                      CoopWS* ws = nullptr, bool active = true, int* cause = nullptr, float* lst = nullptr, int* busy = nullptr) {
   *why = 0;
   int anyB = 0;
   int dead = 0;  // COOP: bail reason latched, the thread keeps pace with its warp until the step ends
@@ -1330,6 +1330,7 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
     float qacc_g[JACO_NV], fcon_g[JACO_NV];
     if (COOP) {
       const bool need = active && !dead && bail != 0;
+      if (need && busy) *busy += 1;   // substeps that left the plain fast path (placement key of the step kernel)
       const int flags = ((bail & (BAIL_OBJ | BAIL_DEST)) ? 0 : COOP_SIMPLE_OBJ) | ((bail & (BAIL_LIMIT | BAIL_OBJ | BAIL_DEST)) ? COOP_FORCE_B : 0);
       // own broad + narrow phase over the arm pairs; stage B only for lanes with something to solve
       LocalSink ks; ks.ncon = 0;
@@ -1461,13 +1462,13 @@ JHD void fast_store(float* state, int N, int i, const FastSim& s) {
 template <bool COOP>
 JHD int entry_step_fast(const JacoCfg& cfg, float* state, int N, int i, int env_id, const float* action_row, float* obs_row,
                         float* reward, unsigned char* done, unsigned char* succ, float* wb, float* term_obs_row, int auto_reset,
-                        float* local_stats, int* needs_reset, int* why, CoopWS* ws = nullptr, bool active = true) {
+                        float* local_stats, int* needs_reset, int* why, CoopWS* ws = nullptr, bool active = true, int* busy = nullptr) {
   FastSim s;
   fast_load(state, N, i, s);
   float obs[JACO_NOBS], r, w; int d, sc;
   *needs_reset = 0;
   int cause = 0;
-  int rc = fast_env_step<COOP>(cfg, s, env_id, action_row, obs, &r, &d, &sc, &w, why, ws, active, &cause, local_stats);
+  int rc = fast_env_step<COOP>(cfg, s, env_id, action_row, obs, &r, &d, &sc, &w, why, ws, active, &cause, local_stats, busy);
   if (!active) return FAST_OK;
   if (rc != FAST_OK) return FAST_BAIL;
   s.accum_rew += r;

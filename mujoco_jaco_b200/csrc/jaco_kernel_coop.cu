@@ -17,18 +17,23 @@ __global__ void __launch_bounds__(JACO_FAST_BLOCK, JACO_FAST_MINBLOCKS) jaco_ste
 
   extern __shared__ __align__(16) unsigned char coop_smem[];
   CoopWS* ws = reinterpret_cast<CoopWS*>(coop_smem) + (threadIdx.x >> 5);
-  const int i0 = blockIdx.x * blockDim.x + threadIdx.x;
-  const bool active = i0 < N;
-  const int i = active ? i0 : N - 1;
+  // Placement: the block's cost per substep is set by the union of the code paths its lanes take, hardly by how many lanes take them.
+  // The envs that needed a rare path last step (cooperative solve, pinv) are therefore dealt round-robin over the first `wave` blocks
+  // (one per SM: they start together and cost what every block cost before), and the remaining blocks hold only quiet envs.
+  int p = blockIdx.x * blockDim.x + threadIdx.x;
+  const int wave = A.wave ? *A.wave : 0;
+  if ((int)blockIdx.x < wave) p = threadIdx.x * wave + blockIdx.x;
+  const bool active = p < N;
+  const int i = A.wave ? A.perm[active ? p : N - 1] : (active ? p : N - 1);
   float local[16];
 #pragma unroll
   for (int k = 0; k < 16; k++) local[k] = 0;
   float a[JACO_NACT];
 #pragma unroll
   for (int k = 0; k < JACO_NACT; k++) a[k] = action[(size_t)i * JACO_NACT + k];
-  float r, w; unsigned char d, sc; int needs_reset, why;
+  float r, w; unsigned char d, sc; int needs_reset, why, busy = 0;
   int rc = entry_step_fast<true>(cfg, state, N, i, env_offset + i, a, obs + (size_t)i * JACO_NOBS, &r, &d, &sc, &w,
-                                 term_obs ? term_obs + (size_t)i * JACO_NOBS : nullptr, auto_reset, local, &needs_reset, &why, ws, active);
+                                 term_obs ? term_obs + (size_t)i * JACO_NOBS : nullptr, auto_reset, local, &needs_reset, &why, ws, active, &busy);
   if (active) {
     if (rc == FAST_OK) {
       reward[i] = r; done[i] = d; succ[i] = sc; wb[i] = w;
@@ -39,7 +44,48 @@ __global__ void __launch_bounds__(JACO_FAST_BLOCK, JACO_FAST_MINBLOCKS) jaco_ste
       atomicAdd(counters + 2 + (bit < 0 ? 0 : bit), 1);
     }
   }
+  // placement key: substeps of this step that left the plain fast path (arm near the scene / joint limit / non-simple scene contacts,
+  // whether or not a cooperative solve followed) + substeps on the pinv branch
+  if (active && A.key) A.key[i] = (unsigned char)fminf((float)busy + local[STAT_PINV], 63.0f);
   block_stats_flush(local, gstats);
+}
+
+// perm = env indices sorted by key (descending; 64 buckets), one block: warp-aggregated shared-memory counting sort.
+// The order inside a bucket is arbitrary: an env's arithmetic does not depend on where it is placed.
+__global__ void __launch_bounds__(1024) jaco_place_kernel(const unsigned char* key, int n, int* perm, int* wave, int lo, int hi, int target, int fixed) {
+  __shared__ int hist[64], off[64];
+  const int tid = threadIdx.x, lane = tid & 31;
+  if (tid < 64) hist[tid] = 0;
+  __syncthreads();
+  for (int e0 = 0; e0 < n; e0 += 1024) {
+    const int e = e0 + tid;
+    const int k = e < n ? key[e] & 63 : 64;
+    const unsigned m = __match_any_sync(0xffffffffu, k);
+    if (k < 64 && lane == __ffs(m) - 1) atomicAdd(&hist[k], __popc(m));
+  }
+  __syncthreads();
+  if (tid == 0) {
+    int run = 0; for (int k = 63; k >= 0; k--) { off[k] = run; run += hist[k]; }
+    const int busy = n - hist[0];
+    int w = (busy + target - 1) / target;
+    w = w < lo ? lo : (w > hi ? hi : w);
+    *wave = fixed >= 0 ? fixed : w;
+  }
+  __syncthreads();
+  for (int e0 = 0; e0 < n; e0 += 1024) {
+    const int e = e0 + tid;
+    const int k = e < n ? key[e] & 63 : 64;
+    const unsigned m = __match_any_sync(0xffffffffu, k);
+    const int leader = __ffs(m) - 1;
+    int base = 0;
+    if (k < 64 && lane == leader) base = atomicAdd(&off[k], __popc(m));
+    base = __shfl_sync(m, base, leader);
+    if (k < 64) perm[base + __popc(m & ((1u << lane) - 1))] = e;
+  }
+}
+cudaError_t jaco_place_launch(const unsigned char* key, int n, int* perm, int* wave, int lo, int hi, int target, int fixed, cudaStream_t st) {
+  jaco_place_kernel<<<1, 1024, 0, st>>>(key, n, perm, wave, lo, hi, target, fixed);
+  return cudaGetLastError();
 }
 
 

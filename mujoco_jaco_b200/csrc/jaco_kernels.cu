@@ -25,6 +25,8 @@ struct jaco_sim_handle {
   int* counters;       // [16]: 0 n_fallback, 1 n_reset, 2..7 bail-reason histogram (cumulative, diagnostics)
   JacoModel* model;    // host copy: the model symbols are per library, a handle re-uploads them when another handle used them last
   long long launches;
+  int* perm; unsigned char* key; int* wave;  // env placement of the step kernel (jaco_launch.h JacoStepArgs); wave: device int
+  int place_lo, place_hi, place_target, place_fixed;
   float* render_prims; int render_cap;   // jaco_render scratch: world primitives of the rendered envs (grown on demand)
   char err[256];
 };
@@ -184,6 +186,25 @@ int jaco_create(const void* model_blob, size_t nbytes, int n_envs, int task_id, 
 #endif
   CK(cudaMalloc(&h->worklist, sizeof(int) * 2 * (size_t)n_envs));
   h->sms = 148; cudaDeviceGetAttribute(&h->sms, cudaDevAttrMultiProcessorCount, device);
+  { /* env placement: the busiest envs are dealt over the first `wave` blocks of the step kernel, ~48 of them per block */
+    const int grid = (n_envs + JACO_FAST_BLOCK - 1) / JACO_FAST_BLOCK;
+    h->place_hi = grid < h->sms ? grid : h->sms; h->place_lo = grid < 24 ? grid : 24; h->place_target = 48; h->place_fixed = grid < 2 ? 0 : -1;
+#ifdef JACO_DIAG
+    if (getenv("JACO_SORT_WAVE")) { h->place_fixed = atoi(getenv("JACO_SORT_WAVE")); if (h->place_fixed > grid) h->place_fixed = grid; }
+    if (getenv("JACO_SORT_TARGET")) h->place_target = atoi(getenv("JACO_SORT_TARGET"));
+#endif
+    CK(cudaMalloc(&h->wave, sizeof(int)));
+    CK(cudaMemset(h->wave, 0, sizeof(int)));
+    CK(cudaMalloc(&h->perm, sizeof(int) * (size_t)n_envs));
+    CK(cudaMalloc(&h->key, (size_t)n_envs));
+    CK(cudaMemset(h->key, 0, (size_t)n_envs));
+    int* iota = (int*)malloc(sizeof(int) * (size_t)n_envs);
+    if (!iota) return JACO_ENOMEM;
+    for (int i = 0; i < n_envs; i++) iota[i] = i;
+    cudaError_t ce = cudaMemcpy(h->perm, iota, sizeof(int) * (size_t)n_envs, cudaMemcpyHostToDevice);
+    free(iota);
+    CK(ce);
+  }
   CK(cudaMalloc(&h->counters, sizeof(int) * 16));
   CK(cudaMemset(h->counters, 0, sizeof(int) * 16));
   CK(cudaMalloc(&h->stats, sizeof(double) * JACO_NSTATS));
@@ -198,7 +219,7 @@ void jaco_destroy(jaco_handle h) {
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
   cudaFree(h->state); cudaFree(h->stats); cudaFree(h->worklist); cudaFree(h->counters);
-  cudaFree(h->render_prims);
+  cudaFree(h->render_prims); cudaFree(h->perm); cudaFree(h->key); cudaFree(h->wave);
   cudaFree(h->s_action); cudaFree(h->s_obs); cudaFree(h->s_reward); cudaFree(h->s_wb); cudaFree(h->s_done); cudaFree(h->s_succ);
   if (g_model_owner == h) g_model_owner = nullptr;
   delete h->model;
@@ -228,9 +249,9 @@ int jaco_render(jaco_handle h, const float* camera19, const float* prim_rgb, int
   cam.znear = camera19[13]; cam.zfar = camera19[14]; cam.ambient = camera19[15];
   if (!(cam.znear > 0) || !(cam.zfar > cam.znear)) { snprintf(h->err, sizeof h->err, "jaco_render: need 0 < znear < zfar"); return JACO_EINVAL; }
   for (int k = 0; k < JACO_RENDER_NPRIM; k++) for (int c = 0; c < 3; c++) cam.rgb[k][c] = prim_rgb[3 * k + c];
-  jaco_render_prims_kernel<<<(env_count + 127) / 128, 128, 0, st>>>(h->state, h->n, env_begin, env_count, h->render_prims);
-  dim3 grid((width + JACO_RENDER_TILE - 1) / JACO_RENDER_TILE, (height + JACO_RENDER_TILE - 1) / JACO_RENDER_TILE, env_count);
-  jaco_render_kernel<<<grid, dim3(JACO_RENDER_TILE, JACO_RENDER_TILE), 0, st>>>(cam, h->render_prims, width, height, rgb, depth);
+  jaco_render_prims_kernel<<<(env_count + 127) / 128, 128, 0, st>>>(cam, h->state, h->n, env_begin, env_count, h->render_prims);
+  dim3 grid((width + JACO_RENDER_TX - 1) / JACO_RENDER_TX, (height + JACO_RENDER_TY - 1) / JACO_RENDER_TY, env_count);
+  jaco_render_kernel<<<grid, dim3(JACO_RENDER_TX, JACO_RENDER_TY), 0, st>>>(cam, h->render_prims, width, height, rgb, depth);
   h->launches += 2;
   CK(cudaGetLastError());
   return JACO_OK;
@@ -258,7 +279,8 @@ int jaco_step(jaco_handle h, const float* action, float* obs, float* reward, uin
   if (!h || !action || !obs || !reward || !done || !succ || !wb) return JACO_EINVAL;
   cudaStream_t st = (cudaStream_t)stream;
   CK(upload_model(h));
-  JacoStepArgs A = {h->cfg, h->state, h->n, h->env_offset, action, obs, reward, done, succ, wb, term_obs, auto_reset, h->stats, h->worklist, h->counters};
+  JacoStepArgs A = {h->cfg, h->state, h->n, h->env_offset, action, obs, reward, done, succ, wb, term_obs, auto_reset, h->stats, h->worklist, h->counters,
+                    h->perm, h->key, h->wave};
   const int nlist = (h->n + JACO_LIST_BLOCK - 1) / JACO_LIST_BLOCK;
   if (h->use_fast == 2) {
     CK(cudaMemsetAsync(h->counters, 0, 2 * sizeof(int), st));
@@ -266,6 +288,9 @@ int jaco_step(jaco_handle h, const float* action, float* obs, float* reward, uin
     jaco_step_list_kernel<<<nlist, JACO_LIST_BLOCK, 0, st>>>(h->cfg, h->state, nullptr, h->n, h->env_offset, action, obs, reward, done, succ, wb,
                                                            term_obs, auto_reset, h->stats, h->worklist, h->counters);
     h->launches += 2;
+    if (h->place_fixed != 0) {   /* next step's placement */
+      CK(jaco_place_launch(h->key, h->n, h->perm, h->wave, h->place_lo, h->place_hi, h->place_target, h->place_fixed, st)); h->launches++;
+    }
   } else {
     jaco_step_kernel<<<nblocks(h->n), JACO_BLOCK, 0, st>>>(h->cfg, h->state, h->n, h->env_offset, action, obs, reward, done, succ, wb, term_obs, auto_reset, h->stats);
     h->launches++;
@@ -290,7 +315,8 @@ int jaco_step_noalloc(jaco_handle h, const float* action, float* obs, float* rew
   CK(upload_model(h));
   int* worklist = scratch;                                  // [2][h->n]
   int* counters = scratch + 2 * JACO_NOALLOC_MAX_ENVS;      // [16] of 64
-  JacoStepArgs A = {h->cfg, h->state, h->n, h->env_offset, action, obs, reward, done, succ, wb, term_obs, auto_reset, h->stats, worklist, counters};
+  JacoStepArgs A = {h->cfg, h->state, h->n, h->env_offset, action, obs, reward, done, succ, wb, term_obs, auto_reset, h->stats, worklist, counters,
+                    h->perm, h->key, nullptr};   /* identity placement: the entry point launches the two step kernels and nothing else */
   const int nlist = (h->n + JACO_LIST_BLOCK - 1) / JACO_LIST_BLOCK;
   CK(cudaMemsetAsync(counters, 0, 16 * sizeof(int), st));   // the array keeps the last call's contents: the list lengths must start at zero
   CK(jaco_coop_launch(A, st));

@@ -7,17 +7,20 @@
 // collision geom (body origins 1-2 and 2-3), flat colour x head-light Lambert term, OpenGL-normalised depth like read_pixels.
 //
 // Two kernels:
-//   jaco_render_prims_kernel  one thread per env: forward kinematics from the SoA state -> world pose of every primitive
-//                             (16 floats each: pos 3, R 9 row-major, size 3, type) in a scratch buffer;
-//   jaco_render_kernel        one 16x16 pixel tile of one env per block: the env's primitives are staged in shared memory, culled
-//                             against the tile's bounding cone (one thread per primitive), then every thread casts its ray against
-//                             the surviving list.  Output: rgb u8 [env][H][W][3] (row 0 = top), depth f32 [env][H][W].
-// Bound: HBM writes (7 B per pixel) once the tile culling has removed most of the 35 intersection tests; bench in scripts/render_bench.py.
+//   jaco_render_prims_kernel  one thread per env: forward kinematics from the SoA state -> world pose of every primitive, then its
+//                             camera-space record (16 floats: camera origin in the primitive's frame 3, R^T Rcam 9, size 3, type) in a
+//                             scratch buffer, so that per pixel a primitive costs 6 FMA for the local ray direction + the hit test;
+//   jaco_render_kernel        one 32x8 pixel tile of one env per block (a warp = one 32-pixel row segment): the env's records are staged
+//                             in shared memory, culled against the tile's bounding cone (one thread per primitive), then every thread
+//                             casts its ray against the surviving list.  Output: rgb u8 [env][H][W][3] (row 0 = top), depth f32 [env][H][W].
+// Bound: instruction issue (about 8 surviving primitives x ~40 instructions per pixel); the HBM floor is 7 B per pixel.
+// scripts/render_bench.py measures it.
 #pragma once
 
 #define JACO_RENDER_NBONE 2
 #define JACO_RENDER_NPRIM (JM_NGEOM + JACO_RENDER_NBONE)
-#define JACO_RENDER_TILE 16
+#define JACO_RENDER_TX 32
+#define JACO_RENDER_TY 8
 
 struct JacoCamera {
   float pos[3], R[9];       // world position; columns of R = camera x (right), y (up), z (backwards: the camera looks along -z), row-major
@@ -56,6 +59,16 @@ JHD void render_prims(JacoSim& s, float* prim) {
     P[12] = 0.04f; P[13] = 0.5f * len; P[14] = 0; P[15] = (float)JACO_GEOM_CAPSULE;
   }
 }
+// camera-space record of a primitive (16 floats): ol[3] = camera origin in the primitive's frame, M[9] = R^T Rcam (row-major: a ray
+// (x, y, -1) of the camera frame has the local direction M (x, y, -1)), size[3], type.  Everything per-pixel work needs; the world
+// normal is not: the Lambert term n . d is invariant under the rotation into the primitive's frame.
+JHD void render_to_camera(const JacoCamera& cam, const float* P, float* Q) {
+  const float* R = P + 3;
+  float r[3] = {cam.pos[0] - P[0], cam.pos[1] - P[1], cam.pos[2] - P[2]};
+  m3tmulv(Q, R, r);
+  for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) Q[3 + 3 * i + j] = R[i] * cam.R[j] + R[3 + i] * cam.R[3 + j] + R[6 + i] * cam.R[6 + j];
+  Q[12] = P[12]; Q[13] = P[13]; Q[14] = P[14]; Q[15] = P[15];
+}
 // bounding-sphere radius of a primitive (plane: negative = unbounded)
 JHD float render_prim_radius(const float* P) {
   const int type = (int)P[15];
@@ -63,23 +76,26 @@ JHD float render_prim_radius(const float* P) {
   if (type == JACO_GEOM_BOX) return sqrtf(P[12] * P[12] + P[13] * P[13] + P[14] * P[14]);
   return P[12] + P[13];
 }
-// ray o + t d (d not normalised; t = distance along the optical axis) against one primitive; t in (tmin, tmax).  Returns true and
-// the hit parameter / world normal when it hits.
-JHD bool render_hit(const float* P, const float* o, const float* d, float tmin, float tmax, float* tout, float* nout) {
-  const float* R = P + 3;
-  float r[3] = {o[0] - P[0], o[1] - P[1], o[2] - P[2]}, ol[3], dl[3];
-  m3tmulv(ol, R, r); m3tmulv(dl, R, d);
-  const int type = (int)P[15];
-  float t = 0, nl[3] = {0, 0, 0};
+// local direction of the camera-frame ray (x, y, -1)
+JHD void render_local_dir(const float* Q, float x, float y, float* dl) {
+  const float* M = Q + 3;
+  for (int k = 0; k < 3; k++) dl[k] = M[3 * k] * x + M[3 * k + 1] * y - M[3 * k + 2];
+}
+// ray ol + t dl (t = distance along the optical axis) against one primitive in its own frame; t in (tmin, tmax).  Returns true with
+// the hit parameter and n . dl (n = outward unit normal at the hit) when it hits.
+JHD bool render_hit(const float* Q, const float* dl, float tmin, float tmax, float* tout, float* ndl) {
+  const float* ol = Q;
+  const int type = (int)Q[15];
+  float t = 0, nd = 0;
   if (type == JACO_GEOM_PLANE) {
     if (!(fabsf(dl[2]) > 1e-12f)) return false;
     t = -ol[2] / dl[2];
     if (!(t > tmin && t < tmax)) return false;
-    nl[2] = ol[2] > 0 ? 1.0f : -1.0f;
+    nd = ol[2] > 0 ? dl[2] : -dl[2];
   } else if (type == JACO_GEOM_BOX) {
     float t0 = tmin, t1 = tmax; int ax = -1; float sg = 0;
     for (int k = 0; k < 3; k++) {
-      const float h = P[12 + k];
+      const float h = Q[12 + k];
       if (fabsf(dl[k]) < 1e-12f) { if (fabsf(ol[k]) > h) return false; continue; }
       const float inv = 1.0f / dl[k];
       float ta = (-h - ol[k]) * inv, tb = (h - ol[k]) * inv, s_ = -1.0f;
@@ -89,16 +105,16 @@ JHD bool render_hit(const float* P, const float* o, const float* d, float tmin, 
       if (t0 > t1) return false;
     }
     if (ax < 0) return false;        // the ray starts inside the box (or before tmin inside it): not drawn
-    t = t0; nl[ax] = sg;
-  } else {                           // capsule: radius P[12], half length P[13] along local z
-    const float rad = P[12], h = P[13];
+    t = t0; nd = sg * dl[ax];
+  } else {                           // capsule: radius Q[12], half length Q[13] along local z
+    const float rad = Q[12], h = Q[13], ir = 1.0f / rad;
     float best = tmax; bool hit = false;
     const float a = dl[0] * dl[0] + dl[1] * dl[1], b = ol[0] * dl[0] + ol[1] * dl[1], c = ol[0] * ol[0] + ol[1] * ol[1] - rad * rad;
     if (a > 1e-12f) {
       const float disc = b * b - a * c;
       if (disc >= 0) {
         const float tc = (-b - sqrtf(disc)) / a, z = ol[2] + tc * dl[2];
-        if (tc > tmin && tc < best && fabsf(z) <= h) { best = tc; hit = true; nl[0] = (ol[0] + tc * dl[0]) / rad; nl[1] = (ol[1] + tc * dl[1]) / rad; nl[2] = 0; }
+        if (tc > tmin && tc < best && fabsf(z) <= h) { best = tc; hit = true; nd = ((ol[0] + tc * dl[0]) * dl[0] + (ol[1] + tc * dl[1]) * dl[1]) * ir; }
       }
     }
     const float dd = a + dl[2] * dl[2];
@@ -106,39 +122,37 @@ JHD bool render_hit(const float* P, const float* o, const float* d, float tmin, 
       const float oz = ol[2] - e * h, bb = b + oz * dl[2], cc = ol[0] * ol[0] + ol[1] * ol[1] + oz * oz - rad * rad, disc = bb * bb - dd * cc;
       if (disc < 0) continue;
       const float ts = (-bb - sqrtf(disc)) / dd, z = oz + ts * dl[2];
-      if (ts > tmin && ts < best && z * e >= 0) { best = ts; hit = true; nl[0] = (ol[0] + ts * dl[0]) / rad; nl[1] = (ol[1] + ts * dl[1]) / rad; nl[2] = z / rad; }
+      if (ts > tmin && ts < best && z * e >= 0) { best = ts; hit = true; nd = ((ol[0] + ts * dl[0]) * dl[0] + (ol[1] + ts * dl[1]) * dl[1] + z * dl[2]) * ir; }
     }
     if (!hit) return false;
     t = best;
   }
-  *tout = t;
-  m3mulv(nout, R, nl);
+  *tout = t; *ndl = nd;
   return true;
 }
-// pixel (row i from the top, column j) -> ray direction in the world, unnormalised, with unit component along the optical axis
-JHD void render_ray(const JacoCamera& cam, int W, int H, float pj, float pi_, float* d) {
+// pixel (row i from the top, column j) -> ray (x, y, -1) in the camera frame
+JHD void render_pixel_xy(const JacoCamera& cam, int W, int H, float pj, float pi_, float* x, float* y) {
   const float ty = cam.tan_half_fovy, tx = ty * (float)W / (float)H;
-  const float x = (2 * pj / W - 1) * tx, y = (1 - 2 * pi_ / H) * ty;
-  for (int k = 0; k < 3; k++) d[k] = cam.R[3 * k] * x + cam.R[3 * k + 1] * y - cam.R[3 * k + 2];
+  *x = (2 * pj / W - 1) * tx; *y = (1 - 2 * pi_ / H) * ty;
 }
-// nearest hit over a primitive list -> colour and OpenGL-normalised depth
-JHD void render_shade(const JacoCamera& cam, const float* prims, const int* list, int nlist, const float* d, unsigned char* rgb, float* depth) {
-  float best = cam.zfar, bn[3] = {0, 0, 0}; int bid = -1;
+// nearest hit over a list of camera-space records -> colour and OpenGL-normalised depth
+JHD void render_shade(const JacoCamera& cam, const float* recs, const int* list, int nlist, float x, float y, unsigned char* rgb, float* depth) {
+  float best = cam.zfar, bnd = 0; int bid = -1;
   for (int k = 0; k < nlist; k++) {
     const int id = list ? list[k] : k;
-    float t, n[3];
-    if (render_hit(prims + 16 * id, cam.pos, d, cam.znear, cam.zfar, &t, n) && (t < best || (t == best && id < bid))) { best = t; bid = id; bn[0] = n[0]; bn[1] = n[1]; bn[2] = n[2]; }
+    float t, nd, dl[3];
+    render_local_dir(recs + 16 * id, x, y, dl);
+    if (render_hit(recs + 16 * id, dl, cam.znear, cam.zfar, &t, &nd) && (t < best || (t == best && id < bid))) { best = t; bid = id; bnd = nd; }
   }
   if (bid < 0) { rgb[0] = rgb[1] = rgb[2] = 0; *depth = 1.0f; return; }
-  const float dn = sqrtf(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
-  float lam = -(bn[0] * d[0] + bn[1] * d[1] + bn[2] * d[2]) / dn;
+  float lam = -bnd / sqrtf(x * x + y * y + 1.0f);
   lam = cam.ambient + (1 - cam.ambient) * fmaxf(lam, 0.0f);
   for (int c = 0; c < 3; c++) rgb[c] = (unsigned char)(fminf(fmaxf(cam.rgb[bid][c] * lam, 0.0f), 1.0f) * 255.0f + 0.5f);
   *depth = (1.0f / cam.znear - 1.0f / best) / (1.0f / cam.znear - 1.0f / cam.zfar);
 }
 
 #ifdef __CUDACC__
-__global__ void __launch_bounds__(128) jaco_render_prims_kernel(const float* state, int N, int env_begin, int env_count, float* prims) {
+__global__ void __launch_bounds__(128) jaco_render_prims_kernel(JacoCamera cam, const float* state, int N, int env_begin, int env_count, float* recs) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= env_count) return;
   JacoSim s;
@@ -146,40 +160,41 @@ __global__ void __launch_bounds__(128) jaco_render_prims_kernel(const float* sta
   for (int k = 0; k < JACO_NQ; k++) s.qpos[k] = state[(size_t)k * N + i];
   float P[JACO_RENDER_NPRIM * 16];
   render_prims(s, P);
-  float* out = prims + (size_t)e * JACO_RENDER_NPRIM * 16;
-  for (int k = 0; k < JACO_RENDER_NPRIM * 16; k++) out[k] = P[k];
+  float* out = recs + (size_t)e * JACO_RENDER_NPRIM * 16;
+  for (int g = 0; g < JACO_RENDER_NPRIM; g++) { float Q[16]; render_to_camera(cam, P + 16 * g, Q); for (int k = 0; k < 16; k++) out[16 * g + k] = Q[k]; }
 }
-// grid = (tiles_x, tiles_y, env_count); block = TILE x TILE threads
-__global__ void __launch_bounds__(JACO_RENDER_TILE * JACO_RENDER_TILE) jaco_render_kernel(JacoCamera cam, const float* prims, int W, int H, unsigned char* rgb, float* depth) {
+// grid = (tiles_x, tiles_y, env_count); block = 32 x 8 threads: a warp is one 32-pixel row segment (128 B of depth, 96 B of rgb)
+__global__ void __launch_bounds__(JACO_RENDER_TX * JACO_RENDER_TY) jaco_render_kernel(JacoCamera cam, const float* recs, int W, int H, unsigned char* rgb, float* depth) {
   __shared__ float sp[JACO_RENDER_NPRIM * 16];
   __shared__ int slist[JACO_RENDER_NPRIM];
   __shared__ unsigned int smask[2];
-  const int tid = threadIdx.y * JACO_RENDER_TILE + threadIdx.x, e = blockIdx.z;
-  const float* P = prims + (size_t)e * JACO_RENDER_NPRIM * 16;
-  for (int k = tid; k < JACO_RENDER_NPRIM * 16; k += JACO_RENDER_TILE * JACO_RENDER_TILE) sp[k] = P[k];
+  const int tid = threadIdx.y * JACO_RENDER_TX + threadIdx.x, e = blockIdx.z;
+  const float* P = recs + (size_t)e * JACO_RENDER_NPRIM * 16;
+  for (int k = tid; k < JACO_RENDER_NPRIM * 16; k += JACO_RENDER_TX * JACO_RENDER_TY) sp[k] = P[k];
   if (tid < 2) smask[tid] = 0;
   __syncthreads();
   // tile culling: bounding sphere of primitive `tid` against the cone around the tile's centre ray that contains its four corners
   if (tid < JACO_RENDER_NPRIM) {
-    const float j0 = blockIdx.x * JACO_RENDER_TILE, i0 = blockIdx.y * JACO_RENDER_TILE;
-    const float j1 = fminf(j0 + JACO_RENDER_TILE, (float)W), i1 = fminf(i0 + JACO_RENDER_TILE, (float)H);
-    float dc[3], dk[3];
-    render_ray(cam, W, H, 0.5f * (j0 + j1), 0.5f * (i0 + i1), dc);
-    const float nc = v3norm(dc);
+    const float j0 = blockIdx.x * JACO_RENDER_TX, i0 = blockIdx.y * JACO_RENDER_TY;
+    const float j1 = fminf(j0 + JACO_RENDER_TX, (float)W), i1 = fminf(i0 + JACO_RENDER_TY, (float)H);
+    float xc, yc, xk, yk;
+    render_pixel_xy(cam, W, H, 0.5f * (j0 + j1), 0.5f * (i0 + i1), &xc, &yc);
+    const float nc = sqrtf(xc * xc + yc * yc + 1.0f);
     float cosa = 1.0f;
-    for (int c = 0; c < 4; c++) { render_ray(cam, W, H, (c & 1) ? j1 : j0, (c & 2) ? i1 : i0, dk); cosa = fminf(cosa, v3dot(dc, dk) / (nc * v3norm(dk))); }
+    for (int c = 0; c < 4; c++) { render_pixel_xy(cam, W, H, (c & 1) ? j1 : j0, (c & 2) ? i1 : i0, &xk, &yk); cosa = fminf(cosa, (xc * xk + yc * yk + 1.0f) / (nc * sqrtf(xk * xk + yk * yk + 1.0f))); }
     cosa = fmaxf(cosa - 1e-4f, -1.0f);              // rounding slack
     const float* Q = sp + 16 * tid;
     const float rad = render_prim_radius(Q);
     bool keep = true;
     if (rad >= 0) {
-      float v[3] = {Q[0] - cam.pos[0], Q[1] - cam.pos[1], Q[2] - cam.pos[2]};
-      const float dist = v3norm(v);
+      float dcl[3];
+      render_local_dir(Q, xc, yc, dcl);             // tile-centre ray in the primitive's frame; the sphere centre is at -ol from the camera
+      const float dist = v3norm(Q);
       if (dist > rad) {
         const float sinb = rad / dist, cosb = sqrtf(fmaxf(1 - sinb * sinb, 0.0f)), sina = sqrtf(fmaxf(1 - cosa * cosa, 0.0f));
         const float cos_ab = cosa * cosb - sina * sinb;           // cos(alpha + beta)
         const bool wide = (cosa * sinb + sina * cosb) < 0 || cos_ab < -0.99f;   // alpha + beta beyond pi: no culling
-        keep = wide || v3dot(v, dc) / (dist * nc) >= cos_ab - 1e-4f;
+        keep = wide || -v3dot(Q, dcl) / (dist * nc) >= cos_ab - 1e-4f;
       }
     }
     if (keep) atomicOr(&smask[tid >> 5], 1u << (tid & 31));
@@ -192,12 +207,12 @@ __global__ void __launch_bounds__(JACO_RENDER_TILE * JACO_RENDER_TILE) jaco_rend
   }
   __syncthreads();
   const int nl = (int)smask[0];
-  const int j = blockIdx.x * JACO_RENDER_TILE + threadIdx.x, i = blockIdx.y * JACO_RENDER_TILE + threadIdx.y;
+  const int j = blockIdx.x * JACO_RENDER_TX + threadIdx.x, i = blockIdx.y * JACO_RENDER_TY + threadIdx.y;
   if (j >= W || i >= H) return;
-  float d[3];
-  render_ray(cam, W, H, j + 0.5f, i + 0.5f, d);
+  float x, y;
+  render_pixel_xy(cam, W, H, j + 0.5f, i + 0.5f, &x, &y);
   unsigned char c3[3]; float z;
-  render_shade(cam, sp, slist, nl, d, c3, &z);
+  render_shade(cam, sp, slist, nl, x, y, c3, &z);
   const size_t pix = ((size_t)e * H + i) * W + j;
   rgb[3 * pix] = c3[0]; rgb[3 * pix + 1] = c3[1]; rgb[3 * pix + 2] = c3[2];
   depth[pix] = z;

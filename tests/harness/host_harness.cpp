@@ -5,6 +5,7 @@
 #define JACO_COLLISION_STATS 1
 #include <vector>
 #include "../../mujoco_jaco_b200/csrc/jaco_fast.cuh"
+#include "../../mujoco_jaco_b200/csrc/jaco_render.cuh"
 
 extern "C" {
 void hh_init(const double* blob) { jaco_model_from_blob(blob, &g_jaco_model_host); }
@@ -12,6 +13,26 @@ static JacoCfg mkcfg(int task, int variant, unsigned long long seed) {
   JacoCfg c; c.task = task; c.variant = variant & 15; c.obs_mode = (variant >> 4) & 15; c.binary = (variant >> 8) & 1; c.seed = seed;
   c.task_max_steps = (task == 0 || task == 1 || task == 5 || task == 6) ? 500 : ((task == 2 || task == 3) ? 700 : 1200);
   return c;
+}
+// the headless camera's per-env and per-pixel code (jaco_render.cuh) without the tile culling: every primitive is tested per pixel
+void hh_render(const float* state, int N, int i, const float* camera19, const float* prim_rgb, int W, int H, unsigned char* rgb, float* depth, float* prims_out) {
+  JacoSim s;
+  for (int k = 0; k < JACO_NQ; k++) s.qpos[k] = state[(size_t)k * N + i];
+  std::vector<float> P(JACO_RENDER_NPRIM * 16);
+  render_prims(s, P.data());
+  if (prims_out) memcpy(prims_out, P.data(), sizeof(float) * P.size());
+  JacoCamera cam;
+  for (int k = 0; k < 3; k++) cam.pos[k] = camera19[k];
+  for (int k = 0; k < 9; k++) cam.R[k] = camera19[3 + k];
+  cam.tan_half_fovy = tanf(0.5f * camera19[12] * 3.14159265358979323846f / 180.0f);
+  cam.znear = camera19[13]; cam.zfar = camera19[14]; cam.ambient = camera19[15];
+  for (int k = 0; k < JACO_RENDER_NPRIM; k++) for (int c = 0; c < 3; c++) cam.rgb[k][c] = prim_rgb[3 * k + c];
+  std::vector<float> Q(JACO_RENDER_NPRIM * 16);
+  for (int g = 0; g < JACO_RENDER_NPRIM; g++) render_to_camera(cam, P.data() + 16 * g, Q.data() + 16 * g);
+  for (int r = 0; r < H; r++) for (int c = 0; c < W; c++) {
+    float x, y; render_pixel_xy(cam, W, H, c + 0.5f, r + 0.5f, &x, &y);
+    render_shade(cam, Q.data(), nullptr, JACO_RENDER_NPRIM, x, y, rgb + 3 * ((size_t)r * W + c), depth + (size_t)r * W + c);
+  }
 }
 void hh_reset(int task, int variant, unsigned long long seed, int env_offset, float* state, int N, float* obs) {
   JacoCfg c = mkcfg(task, variant, seed);

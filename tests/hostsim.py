@@ -103,6 +103,13 @@ class HostSim:
                             fp(wb), int(auto_reset), fp(self.stats), info.ctypes.data_as(C.POINTER(C.c_int)))
         return obs, rew, done, succ, wb, info
 
+    def render(self, i, camera19, palette, W, H):
+        """headless camera of env i through the kernel's per-pixel code (no tile culling): (rgb, depth, prims [35, 16])"""
+        cam, pal = np.ascontiguousarray(camera19, np.float32), np.ascontiguousarray(palette, np.float32)
+        rgb, depth, prims = np.zeros((H, W, 3), np.uint8), np.zeros((H, W), np.float32), np.zeros((len(pal), 16), np.float32)
+        self.L.hh_render(fp(self.state), self.n, i, fp(cam), fp(pal), W, H, rgb.ctypes.data_as(C.POINTER(C.c_ubyte)), fp(depth), fp(prims))
+        return rgb, depth, prims
+
     def get_state(self):
         s = self.state
         return s[:NQ].T.copy(), s[NQ:NQ + NV].T.copy(), s[NQ + NV:].T.copy()
