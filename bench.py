@@ -32,7 +32,7 @@ def _ncu_profile():
     """The committed ncu --set full summary of the step kernel on the aged bench workload (profiles/r02_ncu_step_kernel.json):
     dram bytes per launch and the INSTRUMENTED FP32 operation count (hardware counters: predicated-on thread-level
     FADD + FMUL + 2 x FFMA of one launch = one env step of 65 536 envs)."""
-    for name in ("r02_ncu_step_kernel.json", "r01_ncu_step_kernel.json"):
+    for name in ("r02_final_ncu_step_kernel.json", "r02_ncu_step_kernel.json", "r01_ncu_step_kernel.json"):
         p = os.path.join(REPO, "profiles", name)
         try:
             d = json.load(open(p)); d["file"] = "profiles/" + name

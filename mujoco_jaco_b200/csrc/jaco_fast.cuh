@@ -699,7 +699,7 @@ JHD void rows4_hessian(const Rows4& r, const float e[4][3], const float* M, floa
 
 // Newton on min 0.5 (a - as)' M (a - as) + sum 0.5 D min(0, J a - aref)^2 for one free box (solve_constraints
 // semantics restricted to its 6 dofs).  In: as = qacc_smooth, aw = warm start.  Out: a, fcon = J^T f.
-JHD void fast_solve6(Rows4& r, const FreeBody& fb, const float* as_, const float* aw, float* a, float* fcon) {
+JHD int fast_solve6(Rows4& r, const FreeBody& fb, const float* as_, const float* aw, float* a, float* fcon) {
   float e[4][3], ew[4][3], cw_, cs_, t1_, t2_;
   const float zero4[4][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}, {0, 0, 0}};
 #pragma unroll
@@ -718,7 +718,8 @@ JHD void fast_solve6(Rows4& r, const FreeBody& fb, const float* as_, const float
 #pragma unroll
   for (int k = 0; k < 4; k++) { e[k][0] = usew ? ew[k][0] : e[k][0]; e[k][1] = usew ? ew[k][1] : e[k][1]; e[k][2] = usew ? ew[k][2] : e[k][2]; }
   (void)zero4;
-  for (int it = 0; it < JACO_SOLVER_MAXIT; it++) {
+  int it = 0;
+  for (; it < JACO_SOLVER_MAXIT; it++) {
     float d[6], g[6], jf[6], H[21], p[6];
 #pragma unroll
     for (int i = 0; i < 6; i++) d[i] = a[i] - as_[i];
@@ -761,6 +762,7 @@ JHD void fast_solve6(Rows4& r, const FreeBody& fb, const float* as_, const float
     if (smax <= 2e-7f * fmaxf(1.0f, amax)) break;
   }
   rows4_force(r, e, fcon);
+  return it;
 }
 
 // forward + Euler of one free box whose contacts (if any) are in `c`: updates q7 / v6 / warm6

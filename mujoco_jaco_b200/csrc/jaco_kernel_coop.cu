@@ -8,6 +8,12 @@
 #include "jaco_launch.h"
 #define JACO_COOP_WSN ((JACO_FAST_BLOCK / 32) < JACO_COOP_NWS ? (JACO_FAST_BLOCK / 32) : JACO_COOP_NWS)
 
+#ifdef JACO_DIAG   /* diagnostic builds: start / end time (globaltimer, ns) and SM of every block of the last step kernel launch */
+__device__ unsigned long long g_block_t[3][2048];
+__device__ __forceinline__ unsigned long long jaco_gtime() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+__device__ __forceinline__ unsigned jaco_smid() { unsigned s; asm volatile("mov.u32 %0, %smid;" : "=r"(s)); return s; }
+#endif
+
 // hybrid kernel: fast path per thread + warp-cooperative general contact handling on demand (jaco_coop.cuh);
 // one CoopWS per warp in dynamic shared memory
 __global__ void __launch_bounds__(JACO_FAST_BLOCK, JACO_FAST_MINBLOCKS) jaco_step_coop_kernel(const JacoStepArgs A) {
@@ -15,16 +21,21 @@ __global__ void __launch_bounds__(JACO_FAST_BLOCK, JACO_FAST_MINBLOCKS) jaco_ste
   float* obs = A.obs; float* reward = A.reward; unsigned char* done = A.done; unsigned char* succ = A.succ; float* wb = A.wb;
   float* term_obs = A.term_obs; const int auto_reset = A.auto_reset; double* gstats = A.gstats; int* worklist = A.worklist; int* counters = A.counters;
 
+#ifdef JACO_DIAG
+  if (threadIdx.x == 0 && blockIdx.x < 2048) { g_block_t[0][blockIdx.x] = jaco_gtime(); g_block_t[2][blockIdx.x] = jaco_smid(); }
+#endif
   extern __shared__ __align__(16) unsigned char coop_smem[];
   CoopWS* ws = reinterpret_cast<CoopWS*>(coop_smem) + (threadIdx.x >> 5);
-  // Placement: the block's cost per substep is set by the union of the code paths its lanes take, hardly by how many lanes take them.
-  // The envs that needed a rare path last step (cooperative solve, pinv) are therefore dealt round-robin over the first `wave` blocks
-  // (one per SM: they start together and cost what every block cost before), and the remaining blocks hold only quiet envs.
+  // Placement: a block's cost per substep is set by the union of the code paths its lanes take, hardly by how many lanes
+  // take them.  The envs are served in the order of last step's workload key (perm: solving envs first, then the other busy ones, then
+  // the quiet majority); the first `wave` blocks -- one per SM, they start together -- are dealt that order in snake fashion, so every
+  // one of them gets the same share of every workload level and the busy envs sit in the same warps; the remaining blocks take the tail
+  // of the order contiguously: quiet envs only, close to the uniform-flow rate, in the shadow of the busy blocks' tail.
   int p = blockIdx.x * blockDim.x + threadIdx.x;
-  const int wave = A.wave ? *A.wave : 0;
-  if ((int)blockIdx.x < wave) p = threadIdx.x * wave + blockIdx.x;
+  const int wave = A.wave;
+  if ((int)blockIdx.x < wave) p = threadIdx.x * wave + ((threadIdx.x & 1) ? wave - 1 - (int)blockIdx.x : (int)blockIdx.x);
   const bool active = p < N;
-  const int i = A.wave ? A.perm[active ? p : N - 1] : (active ? p : N - 1);
+  const int i = A.perm ? A.perm[active ? p : N - 1] : (active ? p : N - 1);
   float local[16];
 #pragma unroll
   for (int k = 0; k < 16; k++) local[k] = 0;
@@ -46,13 +57,26 @@ __global__ void __launch_bounds__(JACO_FAST_BLOCK, JACO_FAST_MINBLOCKS) jaco_ste
   }
   // placement key: substeps of this step that left the plain fast path (arm near the scene / joint limit / non-simple scene contacts,
   // whether or not a cooperative solve followed) + substeps on the pinv branch
-  if (active && A.key) A.key[i] = (unsigned char)fminf((float)busy + local[STAT_PINV], 63.0f);
+  // 32..63: the env needed cooperative solves (ordered by how many); 1..31: busy without a solve (near / pinv substeps, 4 per level)
+  if (active && A.key) {
+    const int nb = (int)local[STAT_STAGEB], nq = busy + (int)local[STAT_PINV];
+    A.key[i] = (unsigned char)(nb > 0 ? 32 + min(31, (nb * 31 + 49) / 50) : min(31, (nq + 3) >> 2));
+  }
   block_stats_flush(local, gstats);
+#ifdef JACO_DIAG
+  __syncthreads();
+  if (threadIdx.x == 0 && blockIdx.x < 2048) g_block_t[1][blockIdx.x] = jaco_gtime();
+#endif
 }
+#ifdef JACO_DIAG
+extern "C" int jaco_diag_block_times(unsigned long long* out3x2048) {
+  return cudaMemcpyFromSymbol(out3x2048, g_block_t, sizeof(unsigned long long) * 3 * 2048) == cudaSuccess ? 0 : -2;
+}
+#endif
 
 // perm = env indices sorted by key (descending; 64 buckets), one block: warp-aggregated shared-memory counting sort.
 // The order inside a bucket is arbitrary: an env's arithmetic does not depend on where it is placed.
-__global__ void __launch_bounds__(1024) jaco_place_kernel(const unsigned char* key, int n, int* perm, int* wave, int lo, int hi, int target, int fixed) {
+__global__ void __launch_bounds__(1024) jaco_place_kernel(const unsigned char* key, int n, int* perm, int* dbg) {
   __shared__ int hist[64], off[64];
   const int tid = threadIdx.x, lane = tid & 31;
   if (tid < 64) hist[tid] = 0;
@@ -66,10 +90,12 @@ __global__ void __launch_bounds__(1024) jaco_place_kernel(const unsigned char* k
   __syncthreads();
   if (tid == 0) {
     int run = 0; for (int k = 63; k >= 0; k--) { off[k] = run; run += hist[k]; }
-    const int busy = n - hist[0];
-    int w = (busy + target - 1) / target;
-    w = w < lo ? lo : (w > hi ? hi : w);
-    *wave = fixed >= 0 ? fixed : w;
+    if (dbg) {   // diagnostics (jaco_debug_counters 8..11): quiet envs, busy envs without / with cooperative solves, envs at the top key
+      int nA = 0, nB = 0;
+      for (int k = 32; k < 64; k++) nA += hist[k];
+      for (int k = 1; k < 32; k++) nB += hist[k];
+      dbg[0] = hist[0]; dbg[1] = nB; dbg[2] = nA; dbg[3] = hist[63];
+    }
   }
   __syncthreads();
   for (int e0 = 0; e0 < n; e0 += 1024) {
@@ -83,8 +109,8 @@ __global__ void __launch_bounds__(1024) jaco_place_kernel(const unsigned char* k
     if (k < 64) perm[base + __popc(m & ((1u << lane) - 1))] = e;
   }
 }
-cudaError_t jaco_place_launch(const unsigned char* key, int n, int* perm, int* wave, int lo, int hi, int target, int fixed, cudaStream_t st) {
-  jaco_place_kernel<<<1, 1024, 0, st>>>(key, n, perm, wave, lo, hi, target, fixed);
+cudaError_t jaco_place_launch(const unsigned char* key, int n, int* perm, int* dbg, cudaStream_t st) {
+  jaco_place_kernel<<<1, 1024, 0, st>>>(key, n, perm, dbg);
   return cudaGetLastError();
 }
 

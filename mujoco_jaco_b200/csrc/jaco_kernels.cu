@@ -25,8 +25,7 @@ struct jaco_sim_handle {
   int* counters;       // [16]: 0 n_fallback, 1 n_reset, 2..7 bail-reason histogram (cumulative, diagnostics)
   JacoModel* model;    // host copy: the model symbols are per library, a handle re-uploads them when another handle used them last
   long long launches;
-  int* perm; unsigned char* key; int* wave;  // env placement of the step kernel (jaco_launch.h JacoStepArgs); wave: device int
-  int place_lo, place_hi, place_target, place_fixed;
+  int* perm; unsigned char* key; int wave;   // env placement of the step kernel (jaco_launch.h JacoStepArgs)
   float* render_prims; int render_cap;   // jaco_render scratch: world primitives of the rendered envs (grown on demand)
   char err[256];
 };
@@ -186,15 +185,12 @@ int jaco_create(const void* model_blob, size_t nbytes, int n_envs, int task_id, 
 #endif
   CK(cudaMalloc(&h->worklist, sizeof(int) * 2 * (size_t)n_envs));
   h->sms = 148; cudaDeviceGetAttribute(&h->sms, cudaDevAttrMultiProcessorCount, device);
-  { /* env placement: the busiest envs are dealt over the first `wave` blocks of the step kernel, ~48 of them per block */
+  { /* env placement: on for every handle with at least two blocks; wave = one block per SM */
     const int grid = (n_envs + JACO_FAST_BLOCK - 1) / JACO_FAST_BLOCK;
-    h->place_hi = grid < h->sms ? grid : h->sms; h->place_lo = grid < 24 ? grid : 24; h->place_target = 48; h->place_fixed = grid < 2 ? 0 : -1;
+    h->wave = grid < 2 ? 0 : (grid < h->sms ? grid : h->sms);
 #ifdef JACO_DIAG
-    if (getenv("JACO_SORT_WAVE")) { h->place_fixed = atoi(getenv("JACO_SORT_WAVE")); if (h->place_fixed > grid) h->place_fixed = grid; }
-    if (getenv("JACO_SORT_TARGET")) h->place_target = atoi(getenv("JACO_SORT_TARGET"));
+    if (getenv("JACO_SORT_WAVE")) { int w = atoi(getenv("JACO_SORT_WAVE")); if (w >= 0) h->wave = w > grid ? grid : w; }
 #endif
-    CK(cudaMalloc(&h->wave, sizeof(int)));
-    CK(cudaMemset(h->wave, 0, sizeof(int)));
     CK(cudaMalloc(&h->perm, sizeof(int) * (size_t)n_envs));
     CK(cudaMalloc(&h->key, (size_t)n_envs));
     CK(cudaMemset(h->key, 0, (size_t)n_envs));
@@ -219,7 +215,7 @@ void jaco_destroy(jaco_handle h) {
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
   cudaFree(h->state); cudaFree(h->stats); cudaFree(h->worklist); cudaFree(h->counters);
-  cudaFree(h->render_prims); cudaFree(h->perm); cudaFree(h->key); cudaFree(h->wave);
+  cudaFree(h->render_prims); cudaFree(h->perm); cudaFree(h->key);
   cudaFree(h->s_action); cudaFree(h->s_obs); cudaFree(h->s_reward); cudaFree(h->s_wb); cudaFree(h->s_done); cudaFree(h->s_succ);
   if (g_model_owner == h) g_model_owner = nullptr;
   delete h->model;
@@ -280,7 +276,7 @@ int jaco_step(jaco_handle h, const float* action, float* obs, float* reward, uin
   cudaStream_t st = (cudaStream_t)stream;
   CK(upload_model(h));
   JacoStepArgs A = {h->cfg, h->state, h->n, h->env_offset, action, obs, reward, done, succ, wb, term_obs, auto_reset, h->stats, h->worklist, h->counters,
-                    h->perm, h->key, h->wave};
+                    h->wave > 0 ? h->perm : nullptr, h->key, h->wave};
   const int nlist = (h->n + JACO_LIST_BLOCK - 1) / JACO_LIST_BLOCK;
   if (h->use_fast == 2) {
     CK(cudaMemsetAsync(h->counters, 0, 2 * sizeof(int), st));
@@ -288,9 +284,7 @@ int jaco_step(jaco_handle h, const float* action, float* obs, float* reward, uin
     jaco_step_list_kernel<<<nlist, JACO_LIST_BLOCK, 0, st>>>(h->cfg, h->state, nullptr, h->n, h->env_offset, action, obs, reward, done, succ, wb,
                                                            term_obs, auto_reset, h->stats, h->worklist, h->counters);
     h->launches += 2;
-    if (h->place_fixed != 0) {   /* next step's placement */
-      CK(jaco_place_launch(h->key, h->n, h->perm, h->wave, h->place_lo, h->place_hi, h->place_target, h->place_fixed, st)); h->launches++;
-    }
+    if (h->wave > 0) { CK(jaco_place_launch(h->key, h->n, h->perm, h->counters + 8, st)); h->launches++; }   /* next step's placement */
   } else {
     jaco_step_kernel<<<nblocks(h->n), JACO_BLOCK, 0, st>>>(h->cfg, h->state, h->n, h->env_offset, action, obs, reward, done, succ, wb, term_obs, auto_reset, h->stats);
     h->launches++;
@@ -316,7 +310,7 @@ int jaco_step_noalloc(jaco_handle h, const float* action, float* obs, float* rew
   int* worklist = scratch;                                  // [2][h->n]
   int* counters = scratch + 2 * JACO_NOALLOC_MAX_ENVS;      // [16] of 64
   JacoStepArgs A = {h->cfg, h->state, h->n, h->env_offset, action, obs, reward, done, succ, wb, term_obs, auto_reset, h->stats, worklist, counters,
-                    h->perm, h->key, nullptr};   /* identity placement: the entry point launches the two step kernels and nothing else */
+                    nullptr, h->key, 0};   /* identity placement: the entry point launches the two step kernels and nothing else */
   const int nlist = (h->n + JACO_LIST_BLOCK - 1) / JACO_LIST_BLOCK;
   CK(cudaMemsetAsync(counters, 0, 16 * sizeof(int), st));   // the array keeps the last call's contents: the list lengths must start at zero
   CK(jaco_coop_launch(A, st));

@@ -28,16 +28,15 @@ __device__ __forceinline__ void block_stats_flush(float* local, double* gstats) 
 struct JacoStepArgs {
   JacoCfg cfg; float* state; int N, env_offset; const float* action; float* obs; float* reward;
   unsigned char* done; unsigned char* succ; float* wb; float* term_obs; int auto_reset; double* gstats; int* worklist; int* counters;
-  // env placement: perm[p] = env served by placement slot p, sorted by key (busiest first); key[env] = how many of the
-  // last step's substeps needed a rare path; wave = number of blocks the busiest envs are dealt over (0: identity placement)
-  const int* perm; unsigned char* key; const int* wave;   // wave: device int written by jaco_place_kernel (nullptr: identity placement)
+  // env placement: perm[p] = env served by placement slot p (sorted by key, busiest first; nullptr: identity);
+  // key[env] = workload of the env's last step; wave = number of leading blocks that are dealt the sorted order in snake fashion
+  const int* perm; unsigned char* key; int wave;
 };
 
 // ---- the production step kernel (jaco_kernel_coop.cu)
 cudaError_t jaco_coop_upload_model(const JacoModel* m);
 cudaError_t jaco_coop_launch(const JacoStepArgs& a, cudaStream_t st);
-// perm = envs sorted by key (descending); *wave = number of leading blocks the busiest envs are dealt over, chosen so that each of them
-// gets about `target` envs with a non-zero key, within [lo, hi]; fixed >= 0 overrides (diagnostic builds)
-cudaError_t jaco_place_launch(const unsigned char* key, int n, int* perm, int* wave, int lo, int hi, int target, int fixed, cudaStream_t st);
+// perm = envs sorted by workload key, descending (one block, shared-memory counting sort); dbg (nullable): 4 ints of diagnostics
+cudaError_t jaco_place_launch(const unsigned char* key, int n, int* perm, int* dbg, cudaStream_t st);
 int jaco_coop_prof(unsigned long long* out16);
 
