@@ -608,6 +608,7 @@ JHD JNOINLINE void coop_solve_component(CoopWS& w, int mask) {
     }
     float lo = 0, hi = -1, al = 0, d1, d2, c0;
     coop_rows_cost(w, mask, 0.0f, &c0, &d1, &d2);
+    const float crows0 = c0;   // constraint part of the cost at the current iterate
     float dlo = q1 + d1; const float slope0 = dlo;
     if (!(dlo < 0)) break;
     al = -dlo / (q2 + d2);
@@ -624,6 +625,22 @@ JHD JNOINLINE void coop_solve_component(CoopWS& w, int mask) {
     JPROF_T(i4); JPROF_ADD(14, i4 - i3);
     // ---- update iterate and residuals; per-dof step test
     bool small = true;
+    bool stagnant = false;
+#ifdef JACO_SOLVER_RTOL
+    // mj_solNewton's improvement test (stop when scale * (cost - newcost) < tolerance) in float32 terms: the exact line search lowers
+    // the cost by about -slope0 * al / 2; once that is below JACO_SOLVER_RTOL x the cost itself the iterates only move within float32
+    // rounding of the cost (the float64 tolerance of 1e-8 / scale is far below that resolution).  The step is still taken.
+    {
+      float gauss = 0;
+#ifdef __CUDA_ARCH__
+      const int ln = threadIdx.x & 31;
+      gauss = coop_wsum((ln < JACO_NV && (coop_block(ln) & mask)) ? (w.a[ln] - w.asm_[ln]) * w.Mp[ln] : 0.0f);
+#else
+      for (int i = 0; i < JACO_NV; i++) if (coop_block(i) & mask) gauss += (w.a[i] - w.asm_[i]) * w.Mp[i];
+#endif
+      stagnant = -0.5f * slope0 * al <= JACO_SOLVER_RTOL * (0.5f * gauss + crows0);
+    }
+#endif
 #ifdef __CUDA_ARCH__
     {
       const int ln = threadIdx.x & 31;
@@ -643,7 +660,7 @@ JHD JNOINLINE void coop_solve_component(CoopWS& w, int mask) {
     } COOP_END
     iters = it + 1;
     JPROF_T(i5); JPROF_ADD(15, i5 - i4);
-    if (small) break;
+    if (small || stagnant) break;
   }
   coop_force(w, mask);
   COOP_BEGIN { int i = lane; if (i < JACO_NV && (coop_block(i) & mask)) { w.qacc[i] = w.a[i]; w.fcon[i] = w.jf[i]; } if (lane == 0 && iters > w.iters) w.iters = iters; } COOP_END

@@ -39,6 +39,14 @@ static JacoModel g_jaco_model_host;
                                        // against the oracle; from 12 upwards the results are identical to cap 40 (the solves still running there
                                        // stagnate at float32 resolution: 4.6 % at 16, 1.2 % at 40).  jaco_stats counts the cap hits.
 #endif
+#ifndef JACO_SOLVER_RTOL
+#define JACO_SOLVER_RTOL 2e-8f         // cooperative path: mj_solNewton's improvement test (stop when scale * (cost - newcost) < tolerance) in float32
+                                       // terms -- stop once the exact line search lowers the cost by less than RTOL x the cost (a third of a float32
+                                       // ulp): such iterates only move within rounding.  Without it 3.8 % of the cooperative solves on the in-contact
+                                       // snapshots (1 % on the roll-out) ran into the iteration cap, each a 13-iteration tail that its whole block waits
+                                       // for: 18.1 -> 16.4 ms per step; 2e-8 / 5e-8 keep the GPU parity suite green, 1e-7 puts one carrying env 7e-5 off,
+                                       // 1e-6 flips one touch class of the 4096 snapshots (profiles/r02_solver_rtol_ab.log).
+#endif
 #define JACO_SOLVER_MAXIT_GENERAL 40   // general path: all coupled blocks are solved as one system, which needs more
 #define PK(i, j) ((i) * ((i) + 1) / 2 + (j))  // packed lower-triangular index, j <= i
 

@@ -31,17 +31,14 @@ for w in [int(x) for x in sys.argv[4:]] or [-1, 0]:
     t0 = T[0, :nb].min()
     start = (T[0, :nb] - t0).astype(np.float64) / 1e6
     dur = (T[1, :nb] - T[0, :nb]).astype(np.float64) / 1e6
-    wave = int(cnt[15])
-    busy = start < 0.5           # blocks of the first hardware wave
-    print(f"JACO_SORT_WAVE {w}: busy blocks {wave} (tier A {int(cnt[12])}, tier B {int(cnt[13])}), envs quiet / busy / solving {cnt[8:11].tolist()}, kernel span {(T[1, :nb].max() - t0) / 1e6:.2f} ms", flush=True)
+    wave = 0 if w == 0 else (min(nb, 148) if w < 0 else min(w, nb))     # the library's rule: one first-wave block per SM
+    first = start < 0.5           # blocks of the first hardware wave
+    print(f"JACO_SORT_WAVE {w}: first-wave blocks {wave}, envs quiet / busy / solving / top key {cnt[8:12].tolist()}, kernel span {(T[1, :nb].max() - t0) / 1e6:.2f} ms", flush=True)
     if wave > 0:
-        wa = int(cnt[12])
-        if wa > 0:
-            print(f"  tier-A blocks [0, {wa}): duration mean {dur[:wa].mean():.2f} min {dur[:wa].min():.2f} max {dur[:wa].max():.2f} ms")
-        if wave > wa:
-            print(f"  tier-B blocks [{wa}, {wave}): duration mean {dur[wa:wave].mean():.2f} min {dur[wa:wave].min():.2f} max {dur[wa:wave].max():.2f} ms")
-        print(f"  quiet blocks [{wave}, {nb}): duration mean {dur[wave:].mean():.2f} min {dur[wave:].min():.2f} max {dur[wave:].max():.2f} ms; start mean {start[wave:].mean():.2f} max {start[wave:].max():.2f}")
+        print(f"  first-wave blocks [0, {wave}): duration mean {dur[:wave].mean():.2f} min {dur[:wave].min():.2f} max {dur[:wave].max():.2f} ms")
+        if wave < nb:
+            print(f"  quiet blocks [{wave}, {nb}): duration mean {dur[wave:].mean():.2f} min {dur[wave:].min():.2f} max {dur[wave:].max():.2f} ms; start mean {start[wave:].mean():.2f} max {start[wave:].max():.2f}")
     else:
-        print(f"  all blocks: duration mean {dur.mean():.2f} min {dur.min():.2f} max {dur.max():.2f} ms; first-wave blocks {int(busy.sum())}, late start mean {start[~busy].mean():.2f}")
+        print(f"  all blocks: duration mean {dur.mean():.2f} min {dur.min():.2f} max {dur.max():.2f} ms; first-wave blocks {int(first.sum())}, late start mean {start[~first].mean():.2f}")
     print("  duration deciles:", np.round(np.percentile(dur, [0, 10, 25, 50, 75, 90, 100]), 2).tolist())
     env.close()

@@ -27,6 +27,10 @@ rows = [r for r in csv.reader(l for l in open('gpurun_out/r02_final_launches.csv
 h = rows[0]; ki = h.index('Kernel Name'); vi = h.index('Metric Value')
 for r in rows[1:]: print(r[ki][:40], float(r[vi].replace(',', '')) / 1e6, 'ms')
 P
-timeout 1500 ncu --set full --clock-control none -k regex:jaco_step_coop_kernel --launch-skip 206 -c 1 -f -o $O/r02_final_step python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-contact-rich > $O/ncu_full.log 2>&1; echo "ncu full rc=$?"
+timeout 1500 ncu --set full --metrics smsp__sass_thread_inst_executed_op_fadd_pred_on.sum,smsp__sass_thread_inst_executed_op_fmul_pred_on.sum,smsp__sass_thread_inst_executed_op_ffma_pred_on.sum,smsp__issue_active.avg.pct,smsp__inst_executed_op_local_ld.sum,smsp__inst_executed_op_local_st.sum --clock-control none --import-source on -k regex:jaco_step_coop_kernel --launch-skip 206 -c 1 -f -o $O/r02_final_step python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-contact-rich > $O/ncu_full.log 2>&1; echo "ncu full rc=$?"
 python scripts/ncu_summary.py $O/r02_final_step.ncu-rep 65536 $O/r02_final_ncu_step_kernel.json > $O/ncu_summary.log 2>&1; echo "summary rc=$?"; head -c 1500 $O/r02_final_ncu_step_kernel.json
 ls -la $O/r02_final_step.ncu-rep
+python scripts/ncu_by_function.py $O/r02_final_step.ncu-rep > $O/r02_final_ncu_step_kernel_by_function.txt 2> $O/ncu_by_function.err; head -30 $O/r02_final_ncu_step_kernel_by_function.txt
+python scripts/block_times.py mujoco_jaco_b200/libjaco_b200_diag.so 65536 200 -1 0 > $O/r02_final_block_times.log 2>&1; cat $O/r02_final_block_times.log
+[ "$(stat -c %s $O/r02_final_step.ncu-rep 2>/dev/null || echo 0)" -gt 40000000 ] && rm -f $O/r02_final_step.ncu-rep
+echo done

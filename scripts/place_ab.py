@@ -1,5 +1,5 @@
 """A/B of the step kernel's env placement on the aged picking roll-out: a JACO_DIAG build reads JACO_SORT_WAVE at
-jaco_create (0 = identity placement, w = the busiest envs dealt over the first w blocks).
+jaco_create (0 = identity placement, w = the sorted envs dealt over the first w blocks, -1 = the library's rule: one block per SM).
   python scripts/place_ab.py <lib.so> [envs] [age] [steps] [waves...]"""
 import os
 import sys
@@ -35,5 +35,5 @@ for w in waves:
     timed = [t for k, t in trace if k >= age]
     st = env.stats().cpu().numpy()
     print(f"wave {w:4d}: ms/step (age {age}) mean {sum(timed) / len(timed):7.2f} min {min(timed):7.2f} max {max(timed):7.2f} | "
-          f"trace {[(k, round(t, 1)) for k, t in trace if k < age]} | quiet, busy, solving, key63, wA, wB, -, wA+wB {env.debug_counters()[8:16].tolist()} | episodes {st[0]:.0f} stageB {st[11] / st[7] / 50:.4f} pinv {st[12] / st[7] / 50:.4f}", flush=True)
+          f"trace {[(k, round(t, 1)) for k, t in trace if k < age]} | envs quiet / busy / solving / top key {env.debug_counters()[8:12].tolist()} | episodes {st[0]:.0f} stageB {st[11] / st[7] / 50:.4f} pinv {st[12] / st[7] / 50:.4f}", flush=True)
     env.close()
