@@ -217,9 +217,8 @@ def main():
     for i in range(W):
         env.step(act(i))
     env.stats(clear=True)
-    sampler = ClockSampler(local) if rank == 0 else None
-    if sampler:
-        sampler.start()
+    sampler = ClockSampler(local)      # every rank samples its own GPU (per_rank table); rank 0's summary is the line's `clocks`
+    sampler.start()
     # L2 is flushed between timed iterations (a 256 MB fill, outside the per-step event pairs): the state working set
     # (30 MB) would otherwise stay resident in the 126 MB L2 from one step to the next
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
@@ -293,9 +292,10 @@ def main():
                         "workload": f"4096 in-contact snapshots (tests/golden/contact_snapshots.npz) tiled to {n} envs, re-injected before every step",
                         "contact_fraction": float(cs[13]) / (n * 50), "stageB_fraction": float(cs[11]) / (n * 50),
                         "iteration_cap_hits": float(cs[10]), "contact_cap_hits": float(cs[9])}
-    if sampler:
-        sampler.stop_flag = True
-        sampler.join(timeout=2)
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+    clk = sampler.summary()
+    per_rank_hw = gather_per_rank(torch.tensor([min(kernel_ms), max(kernel_ms), float(clk["sm_mhz"] or 0), float(len(clk["reasons"]))], device=dev))
 
     if rank == 0:
         peaks, which = _peaks()
@@ -352,9 +352,11 @@ def main():
                               "contact_cap_hits": float(st[9]), "iteration_cap_hits": float(st[10]),
                               "general_path_fallbacks": float(st[14]), "general_resets": float(st[15])},
             "per_rank": {"ms_per_step": [r[0] for r in per_rank], "stageB_fraction": [r[1] for r in per_rank],
-                         "pinv_fraction": [r[2] for r in per_rank], "contact_fraction": [r[3] for r in per_rank], "episodes": [r[4] for r in per_rank]},
+                         "pinv_fraction": [r[2] for r in per_rank], "contact_fraction": [r[3] for r in per_rank], "episodes": [r[4] for r in per_rank],
+                         "ms_per_step_min": [r[0] for r in per_rank_hw], "ms_per_step_max": [r[1] for r in per_rank_hw],
+                         "sm_mhz": [r[2] for r in per_rank_hw], "throttle_reasons": [r[3] for r in per_rank_hw]},
             "contact_rich": contact_rich,
-            "clocks": sampler.summary() if sampler else None,
+            "clocks": clk,
         }
         if not args.no_cpu_baseline and world == 1 and policy is None:
             out["cpu_baseline"] = cpu_baseline(args.cpu_seconds)

@@ -101,7 +101,9 @@ int jaco_render(jaco_handle h, const float* camera19, const float* prim_rgb, int
                 uint8_t* rgb, float* depth, void* stream);
 
 /* diagnostics: host copy of the step work-list counters, out int32[16] = {n_bail, n_reset of the last step,
- * cumulative bail-reason histogram (limit, hand, forearm, object, dest, osc, nan), ...}; synchronises the device. */
+ * cumulative bail-reason histogram (limit, hand, forearm, object, dest, osc), 8..11: env placement of the step kernel:
+ * envs that were quiet / busy without a cooperative solve / busy with one / at the top workload key in the last step};
+ * synchronises the device. */
 int jaco_debug_counters(jaco_handle h, int32_t* out16);
 int jaco_n_envs(jaco_handle h);
 /* number of kernels this handle has launched (bench.py "gpu_launches") */

@@ -1372,6 +1372,9 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
           const CoopWS& wt = wsbase[slot - base];
           solved = wt.solved;
           if (solved) { for (int i = 0; i < JACO_NV; i++) { qacc_g[i] = wt.qacc[i]; fcon_g[i] = wt.fcon[i]; } if (it == 49) s.touch_now = touch_class(wt.touch); }
+#if defined(JACO_DIAG) && defined(__CUDA_ARCH__)
+          if (busy) { busy[1] += wt.iters; busy[2] = max(busy[2], wt.ncon); busy[3] += (wt.iters >= JACO_SOLVER_MAXIT); }   // per-env solve cost (diagnostics)
+#endif
           if (lst) {   // workload / cap counters (jaco_stats)
             lst[STAT_STAGEB] += 1;
             if (wt.ncon >= JACO_MAXCON) lst[STAT_CONCAP] += 1;

@@ -10,6 +10,7 @@
 
 #ifdef JACO_DIAG   /* diagnostic builds: start / end time (globaltimer, ns) and SM of every block of the last step kernel launch */
 __device__ unsigned long long g_block_t[3][2048];
+__device__ int g_env_dbg[4][65536];   // per env of the last launch (first 65536): block, solve iterations (sum), max contacts, cap hits
 __device__ __forceinline__ unsigned long long jaco_gtime() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 __device__ __forceinline__ unsigned jaco_smid() { unsigned s; asm volatile("mov.u32 %0, %smid;" : "=r"(s)); return s; }
 #endif
@@ -42,9 +43,9 @@ __global__ void __launch_bounds__(JACO_FAST_BLOCK, JACO_FAST_MINBLOCKS) jaco_ste
   float a[JACO_NACT];
 #pragma unroll
   for (int k = 0; k < JACO_NACT; k++) a[k] = action[(size_t)i * JACO_NACT + k];
-  float r, w; unsigned char d, sc; int needs_reset, why, busy = 0;
+  float r, w; unsigned char d, sc; int needs_reset, why, busy[4] = {0, 0, 0, 0};
   int rc = entry_step_fast<true>(cfg, state, N, i, env_offset + i, a, obs + (size_t)i * JACO_NOBS, &r, &d, &sc, &w,
-                                 term_obs ? term_obs + (size_t)i * JACO_NOBS : nullptr, auto_reset, local, &needs_reset, &why, ws, active, &busy);
+                                 term_obs ? term_obs + (size_t)i * JACO_NOBS : nullptr, auto_reset, local, &needs_reset, &why, ws, active, busy);
   if (active) {
     if (rc == FAST_OK) {
       reward[i] = r; done[i] = d; succ[i] = sc; wb[i] = w;
@@ -59,16 +60,20 @@ __global__ void __launch_bounds__(JACO_FAST_BLOCK, JACO_FAST_MINBLOCKS) jaco_ste
   // whether or not a cooperative solve followed) + substeps on the pinv branch
   // 32..63: the env needed cooperative solves (ordered by how many); 1..31: busy without a solve (near / pinv substeps, 4 per level)
   if (active && A.key) {
-    const int nb = (int)local[STAT_STAGEB], nq = busy + (int)local[STAT_PINV];
+    const int nb = (int)local[STAT_STAGEB], nq = busy[0] + (int)local[STAT_PINV];
     A.key[i] = (unsigned char)(nb > 0 ? 32 + min(31, (nb * 31 + 49) / 50) : min(31, (nq + 3) >> 2));
   }
   block_stats_flush(local, gstats);
 #ifdef JACO_DIAG
+  if (active && i < 65536) { g_env_dbg[0][i] = blockIdx.x; g_env_dbg[1][i] = busy[1]; g_env_dbg[2][i] = busy[2]; g_env_dbg[3][i] = busy[3] + 1000 * (int)local[STAT_STAGEB] + 100000 * (int)local[STAT_PINV]; }
   __syncthreads();
   if (threadIdx.x == 0 && blockIdx.x < 2048) g_block_t[1][blockIdx.x] = jaco_gtime();
 #endif
 }
 #ifdef JACO_DIAG
+extern "C" int jaco_diag_env_dbg(int* out4x65536) {
+  return cudaMemcpyFromSymbol(out4x65536, g_env_dbg, sizeof(int) * 4 * 65536) == cudaSuccess ? 0 : -2;
+}
 extern "C" int jaco_diag_block_times(unsigned long long* out3x2048) {
   return cudaMemcpyFromSymbol(out3x2048, g_block_t, sizeof(unsigned long long) * 3 * 2048) == cudaSuccess ? 0 : -2;
 }
