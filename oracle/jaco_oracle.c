@@ -1332,6 +1332,14 @@ int jo_render_prims(jo_env *e, double *out, int maxprim) {
   }
   return n;
 }
+/* the constraint problem of the last forward, for independent optimality checks (tests/test_oracle_independent.py):
+ * J [nefc][NV], D, aref, qacc_smooth; returns nefc */
+int jo_get_efc(const jo_env *e, double *J, double *D, double *aref, double *qacc_smooth, int maxrows) {
+  int n = e->nefc < maxrows ? e->nefc : maxrows;
+  for (int r = 0; r < n; r++) { for (int i = 0; i < NV; i++) J[r * NV + i] = e->efc_J[r][i]; D[r] = e->efc_D[r]; aref[r] = e->efc_aref[r]; }
+  for (int i = 0; i < NV; i++) qacc_smooth[i] = e->qacc_smooth[i];
+  return e->nefc;
+}
 int jo_get_contacts(const jo_env *e, double *out, int maxcon) {
   int n = e->ncon < maxcon ? e->ncon : maxcon;
   for (int c = 0; c < n; c++) {

@@ -60,6 +60,8 @@ def lib(f32=False, fast=False):
         L.jo_forward.argtypes = [C.c_void_p, _dp, _dp, _dp, _dp, _dp, _dp, _dp, _ip, _dp]
         L.jo_get_contacts.argtypes = [C.c_void_p, _dp, C.c_int]
         L.jo_get_contacts.restype = C.c_int
+        L.jo_get_efc.argtypes = [C.c_void_p, _dp, _dp, _dp, _dp, C.c_int]
+        L.jo_get_efc.restype = C.c_int
         L.jo_render_prims.argtypes = [C.c_void_p, _dp, C.c_int]
         L.jo_render_prims.restype = C.c_int
         L.jo_osc.argtypes = [C.c_void_p] + [_dp] * 8
@@ -138,6 +140,13 @@ class OracleEnv:
         out = np.zeros((maxcon, 10))
         n = self.L.jo_get_contacts(self.h, _d(out), maxcon)
         return out[:n]
+
+    def efc(self, maxrows=1024):
+        """constraint problem of the last forward: (J [nefc, 21], D, aref, qacc_smooth)"""
+        J, D, aref, qs = np.zeros((maxrows, NV)), np.zeros(maxrows), np.zeros(maxrows), np.zeros(NV)
+        n = self.L.jo_get_efc(self.h, _d(J), _d(D), _d(aref), _d(qs), maxrows)
+        assert n <= maxrows
+        return J[:n], D[:n], aref[:n], qs
 
     def render_prims(self, maxprim=64):
         """world primitives of the headless camera at the current qpos: float64 [n, 16] = pos 3, R 9 (row-major), size 3, type"""
