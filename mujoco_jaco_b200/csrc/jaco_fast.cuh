@@ -926,8 +926,13 @@ struct LocalPoses {
   const float* bx[JACO_NBODY];
   const float* bR[JACO_NBODY];
 };
-// cand_out != nullptr: stop after stage A and return the candidate-pair mask (the device path hands the narrow phase
-// to the block's collision queue); nullptr: also run the narrow phase here (CPU harness, same contacts).
+// cand_out != nullptr: when more than FAST_DEFER_PAIRS candidate pairs survive stage A, stop there, return their mask and k.ncon = -1:
+// the caller hands the narrow phase of such an env to the cooperative path (lanes over pairs, same collide_pair, same contact order)
+// instead of running 20+ box-box tests one after the other on the owner thread -- one arm lying across the scene (28 contacts) made
+// its whole block 7 ms late.  nullptr: always run the narrow phase here (CPU harness, in-place reset).
+#ifndef FAST_DEFER_PAIRS
+#define FAST_DEFER_PAIRS 6
+#endif
 JHD JNOINLINE void fast_arm_collide(const ChainOut& c, const FreeBody& fo, const FreeBody& fd, LocalSink& k, unsigned long long* cand_out = nullptr) {
   const JacoModel& m = MDL;
   const float Z3[3] = {0, 0, 0}, I9[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
@@ -1033,7 +1038,9 @@ JHD JNOINLINE void fast_arm_collide(const ChainOut& c, const FreeBody& fo, const
   }
   FAST_WSTAT(11);
   if (cand) FAST_WSTAT(12);
-  if (cand_out) { *cand_out = cand; return; }
+#ifdef __CUDA_ARCH__
+  if (cand_out && __popcll(cand) > FAST_DEFER_PAIRS) { *cand_out = cand; k.ncon = -1; return; }
+#endif
   if (!cand) return;
   if (JACO_TIMING_SKIP & 4) { k.ncon = (int)(cand >> 63); return; }
   // ---- narrow phase, one routine at a time so that lanes working on different pairs stay converged
@@ -1336,8 +1343,12 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
       const int flags = ((bail & (BAIL_OBJ | BAIL_DEST)) ? 0 : COOP_SIMPLE_OBJ) | ((bail & (BAIL_LIMIT | BAIL_OBJ | BAIL_DEST)) ? COOP_FORCE_B : 0);
       // own broad + narrow phase over the arm pairs; stage B only for lanes with something to solve
       LocalSink ks; ks.ncon = 0;
-      if (!(JACO_TIMING_SKIP & 2) && need && (bail & (BAIL_HAND | BAIL_FOREARM))) fast_arm_collide(f.c, f.fo, f.fd, ks);
-      const bool needB = !(JACO_TIMING_SKIP & 1) && need && (ks.ncon > 0 || (flags & COOP_FORCE_B));
+      unsigned long long cand_def = 0;   // != 0: the narrow phase of this env's arm pairs is deferred to the cooperative path
+      if (!(JACO_TIMING_SKIP & 2) && need && (bail & (BAIL_HAND | BAIL_FOREARM))) {
+        fast_arm_collide(f.c, f.fo, f.fd, ks, &cand_def);
+        if (ks.ncon < 0) ks.ncon = 0; else cand_def = 0;
+      }
+      const bool needB = !(JACO_TIMING_SKIP & 1) && need && (ks.ncon > 0 || cand_def != 0 || (flags & COOP_FORCE_B));
       FAST_WSTAT(0);
       if (need) { FAST_WSTAT(1); if (bail & BAIL_LIMIT) FAST_WSTAT(8); if (bail & (BAIL_HAND | BAIL_FOREARM)) FAST_WSTAT(9); if (bail & (BAIL_OBJ | BAIL_DEST)) FAST_WSTAT(10); }
 #ifdef __CUDA_ARCH__
@@ -1358,7 +1369,10 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
       for (int base = 0; base < ntask; base += nwarps) {
         const bool mine = slot >= base && slot < base + nwarps;
         JPROF_T(t1);
-        if (mine) { CoopWS& wt = wsbase[slot - base]; coop_publish(wt, s, f.c, f.fo, f.fd, f.fsm, it == 49); coop_publish_contacts(wt, ks, flags); }
+        if (mine) {
+          CoopWS& wt = wsbase[slot - base]; coop_publish(wt, s, f.c, f.fo, f.fd, f.fsm, it == 49); coop_publish_contacts(wt, ks, flags);
+          if (cand_def) { wt.cand[0] |= (unsigned)(cand_def & 0xFFFFFFFFull); wt.cand[1] = (unsigned)(cand_def >> 32); }   // lanes collide these pairs
+        }
         __syncthreads();
         JPROF_T(t2);
         if (mywarp < nwarps && base + mywarp < ntask) {
@@ -1377,7 +1391,7 @@ JHD int fast_env_step(const JacoCfg& cfg, FastSim& s, int env_id, const float* a
 #endif
           if (lst) {   // workload / cap counters (jaco_stats)
             lst[STAT_STAGEB] += 1;
-            if (wt.ncon >= JACO_MAXCON) lst[STAT_CONCAP] += 1;
+            if (wt.ncon >= JACO_MAXCON || ks.ncon >= LocalSink::MAXC) lst[STAT_CONCAP] += 1;   // incl. the owner thread's 24 arm contacts
             if (wt.iters >= JACO_SOLVER_MAXIT) lst[STAT_ITERCAP] += 1;
             if (wt.fingerobj) lst[STAT_FINGEROBJ] += 1;
           }
