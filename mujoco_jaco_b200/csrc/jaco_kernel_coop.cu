@@ -131,6 +131,10 @@ cudaError_t jaco_coop_launch(const JacoStepArgs& a, cudaStream_t st) {
   jaco_step_coop_kernel<<<(a.N + JACO_FAST_BLOCK - 1) / JACO_FAST_BLOCK, JACO_FAST_BLOCK, smem, st>>>(a);
   return cudaGetLastError();
 }
+#ifdef JACO_PROF
+extern "C" int jaco_debug_prof(unsigned long long* out16);   /* profiling builds: what scripts/prof_coop.py reads */
+int jaco_debug_prof(unsigned long long* out16) { return jaco_coop_prof(out16); }
+#endif
 int jaco_coop_prof(unsigned long long* out16) {
 #ifdef JACO_PROF
   return cudaMemcpyFromSymbol(out16, g_jprof, 16 * sizeof(unsigned long long)) == cudaSuccess ? 0 : -2;
